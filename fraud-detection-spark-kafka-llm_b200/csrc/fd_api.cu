@@ -1,0 +1,277 @@
+// fd_api.cu -- the extern "C" boundary (include/fdb200.h): handle lifetime, model upload, and the
+// host-side orchestration of the kernels in fd_rows.cu / fd_score.cu / fd_train.cu.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <vector>
+
+#include "fd_rows.cuh"
+
+namespace fd {
+
+int set_err(fd_handle* h, int code, const char* fmt, ...) {
+    if (h) {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof(buf), fmt, ap);
+        va_end(ap);
+        h->err = buf;
+    }
+    return code;
+}
+
+int cuda_fail(fd_handle* h, cudaError_t e, const char* what) {
+    return set_err(h, FD_ERR_CUDA, "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+}
+
+// grow the handle-owned workspace (contents are lost when it moves)
+int ensure_ws(fd_handle* h, size_t bytes) {
+    if (bytes <= h->ws_bytes) return FD_OK;
+    if (h->ws) {
+        FD_CUDA(h, cudaDeviceSynchronize());
+        FD_CUDA(h, cudaFree(h->ws));
+        h->ws = nullptr;
+        h->ws_bytes = 0;
+    }
+    bytes = (bytes + (size_t)(1 << 20) - 1) & ~(size_t)((1 << 20) - 1);
+    FD_CUDA(h, cudaMalloc((void**)&h->ws, bytes));
+    h->ws_bytes = bytes;
+    h->feat_rows = -1;
+    FD_CUDA(h, cudaMemset(h->ws, 0, 256));
+    return FD_OK;
+}
+
+template <typename T>
+static int upload(fd_handle* h, T** dst, const T* src, size_t n) {
+    if (*dst) {
+        FD_CUDA(h, cudaFree(*dst));
+        *dst = nullptr;
+    }
+    if (n == 0) return FD_OK;
+    FD_CUDA(h, cudaMalloc((void**)dst, n * sizeof(T)));
+    FD_CUDA(h, cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+    return FD_OK;
+}
+
+}  // namespace fd
+
+using namespace fd;
+
+extern "C" {
+
+int fd_version(void) { return 100; }
+
+int fd_create(int device, fd_handle** out) {
+    if (!out) return FD_ERR_INVALID;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return FD_ERR_CUDA;
+    fd_handle* h = new fd_handle();
+    h->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) {
+        delete h;
+        return FD_ERR_CUDA;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) h->sm_count = prop.multiProcessorCount;
+    *out = h;
+    return FD_OK;
+}
+
+int fd_destroy(fd_handle* h) {
+    if (!h) return FD_OK;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    Model& m = h->m;
+    cudaFree(m.sw_slots);
+    cudaFree(m.sw_pool);
+    cudaFree(m.idf);
+    cudaFree(m.coef);
+    cudaFree(m.nodes);
+    cudaFree(m.roots);
+    cudaFree(m.leaf2);
+    cudaFree(m.tree_w);
+    cudaFree(h->ws);
+    for (int i = 0; i < 3; ++i) {
+        if (h->hbuf[i]) cudaFree(h->hbuf[i]);
+        if (h->hs[i]) cudaStreamDestroy(h->hs[i]);
+        if (h->hev[i]) cudaEventDestroy(h->hev[i]);
+    }
+    if (h->pinned_ctrl) cudaFreeHost(h->pinned_ctrl);
+    delete h;
+    return FD_OK;
+}
+
+const char* fd_last_error(fd_handle* h) { return h ? h->err.c_str() : "null handle"; }
+
+int64_t fd_launch_count(fd_handle* h) { return h ? h->launches : 0; }
+
+int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, int32_t n_words, int32_t case_sensitive) {
+    if (!h || n_words < 0 || (n_words > 0 && (!words || !offs))) return set_err(h, FD_ERR_INVALID, "bad stop-word arguments");
+    FD_CUDA(h, cudaSetDevice(h->device));
+    Model& m = h->m;
+    m.empty_is_stop = 0;
+    if (n_words == 0) {
+        if (m.sw_slots) cudaFree(m.sw_slots);
+        if (m.sw_pool) cudaFree(m.sw_pool);
+        m.sw_slots = nullptr;
+        m.sw_pool = nullptr;
+        m.sw_cap = 0;
+        return FD_OK;
+    }
+    if (n_words > 2048) return set_err(h, FD_ERR_LIMIT, "at most 2048 stop words are supported (got %d)", n_words);
+    int cap = 16;
+    while (cap < 2 * n_words) cap <<= 1;
+    std::vector<uint4> slots(cap, make_uint4(0xFFFFFFFFu, 0, 0, 0));
+    std::vector<uint8_t> pool;
+    for (int i = 0; i < n_words; ++i) {
+        const int len = offs[i + 1] - offs[i];
+        if (len < 0) return set_err(h, FD_ERR_INVALID, "stop-word offsets not ascending");
+        std::vector<uint8_t> w(words + offs[i], words + offs[i] + len);
+        if (!case_sensitive)
+            for (auto& c : w)
+                if (c >= 'A' && c <= 'Z') c |= 0x20;
+        if (len == 0) {
+            m.empty_is_stop = 1;
+            continue;
+        }
+        const uint32_t hsh = murmur3_host(w.data(), len);
+        uint4 s;
+        if (len <= 12) {
+            uint32_t b[3] = {0, 0, 0};
+            for (int k = 0; k < len; ++k) b[k >> 2] |= (uint32_t)w[k] << (8 * (k & 3));
+            s = make_uint4((uint32_t)len, b[0], b[1], b[2]);
+        } else {
+            s = make_uint4((uint32_t)len | 0x80000000u, (uint32_t)pool.size(), 0, 0);
+            pool.insert(pool.end(), w.begin(), w.end());
+        }
+        uint32_t slot = hsh & (uint32_t)(cap - 1);
+        while (slots[slot].x != 0xFFFFFFFFu) slot = (slot + 1) & (uint32_t)(cap - 1);
+        slots[slot] = s;
+    }
+    int rc = upload(h, &m.sw_slots, slots.data(), slots.size());
+    if (rc) return rc;
+    rc = upload(h, &m.sw_pool, pool.data(), pool.size());
+    if (rc) return rc;
+    m.sw_cap = cap;
+    return FD_OK;
+}
+
+int fd_hash_terms(const uint8_t* terms, const int32_t* offs, int32_t n, int32_t num_features, int32_t* out) {
+    if (n < 0 || num_features <= 0 || (n > 0 && (!offs || !out))) return FD_ERR_INVALID;
+    for (int i = 0; i < n; ++i) {
+        const int len = offs[i + 1] - offs[i];
+        if (len < 0) return FD_ERR_INVALID;
+        out[i] = (int32_t)nonneg_mod_host(murmur3_host(terms + offs[i], len), num_features);
+    }
+    return FD_OK;
+}
+
+int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary) {
+    if (!h || num_features <= 0) return set_err(h, FD_ERR_INVALID, "numFeatures must be > 0");
+    Model& m = h->m;
+    m.num_features = num_features;
+    m.binary = binary ? 1 : 0;
+    m.mod_pow2 = (num_features & (num_features - 1)) == 0;
+    m.mod_magic = m.mod_pow2 ? 0u : (uint32_t)((1ULL << 32) / (uint64_t)num_features);
+    m.mod_r32 = (uint32_t)((1ULL << 32) % (uint64_t)num_features);
+    m.empty_idx = nonneg_mod_host(murmur3_host(nullptr, 0), num_features);
+    return FD_OK;
+}
+
+int fd_set_idf(fd_handle* h, const double* idf, int32_t num_features) {
+    if (!h) return FD_ERR_INVALID;
+    FD_CUDA(h, cudaSetDevice(h->device));
+    if (!idf) return upload(h, &h->m.idf, (const double*)nullptr, 0);
+    if (num_features != h->m.num_features)
+        return set_err(h, FD_ERR_INVALID, "idf size %d != numFeatures %d", num_features, h->m.num_features);
+    return upload(h, &h->m.idf, idf, (size_t)num_features);
+}
+
+int fd_set_linear(fd_handle* h, const double* coef_dense, int32_t num_features, double intercept, double threshold) {
+    if (!h || !coef_dense) return set_err(h, FD_ERR_INVALID, "null coefficients");
+    if (num_features != h->m.num_features)
+        return set_err(h, FD_ERR_INVALID, "coefficient size %d != numFeatures %d", num_features, h->m.num_features);
+    FD_CUDA(h, cudaSetDevice(h->device));
+    int rc = upload(h, &h->m.coef, coef_dense, (size_t)num_features);
+    if (rc) return rc;
+    h->m.intercept = intercept;
+    // LogisticRegressionModel.raw2prediction: rawThreshold = log(t / (1 - t)), -inf at 0, +inf at 1
+    h->m.raw_threshold = threshold <= 0.0 ? -INFINITY : (threshold >= 1.0 ? INFINITY : std::log(threshold / (1.0 - threshold)));
+    h->m.classifier = 1;
+    h->m.n_classes = 2;
+    return FD_OK;
+}
+
+int fd_set_forest(fd_handle* h, int32_t kind, int32_t n_trees, const int32_t* tree_offsets, const int32_t* feature,
+                  const double* threshold, const int32_t* left, const int32_t* right, const double* leaf_value,
+                  const double* tree_weights, int32_t n_classes) {
+    if (!h) return FD_ERR_INVALID;
+    if (kind != FD_KIND_DT && kind != FD_KIND_RF && kind != FD_KIND_GBT) return set_err(h, FD_ERR_INVALID, "unknown forest kind %d", kind);
+    if (n_trees <= 0 || !tree_offsets || !feature || !threshold || !left || !right || !leaf_value)
+        return set_err(h, FD_ERR_INVALID, "null forest arrays");
+    if (n_classes != 2) return set_err(h, FD_ERR_INVALID, "binary classification only on this path (numClasses = %d)", n_classes);
+    if (kind == FD_KIND_DT && n_trees != 1) return set_err(h, FD_ERR_INVALID, "a decision tree model has one tree");
+    if (kind == FD_KIND_GBT && !tree_weights) return set_err(h, FD_ERR_INVALID, "GBT needs tree weights");
+    FD_CUDA(h, cudaSetDevice(h->device));
+    const int total = tree_offsets[n_trees];
+    std::vector<Node> nodes((size_t)total);
+    std::vector<double2> leaf2((size_t)total, make_double2(0.0, 0.0));
+    std::vector<int32_t> roots((size_t)n_trees);
+    std::vector<std::pair<int, int>> queue;
+    for (int t = 0; t < n_trees; ++t) {
+        const int base = tree_offsets[t], cnt = tree_offsets[t + 1] - base;
+        if (cnt <= 0) return set_err(h, FD_ERR_INVALID, "tree %d has no nodes", t);
+        roots[t] = base;
+        int next = base + 1;
+        queue.clear();
+        queue.push_back({0, base});
+        for (size_t qi = 0; qi < queue.size(); ++qi) {
+            const int o = queue[qi].first, n = queue[qi].second;
+            const int go = base + o;
+            if (feature[go] < 0) {
+                nodes[n].feat = -1;
+                nodes[n].child = n;
+                nodes[n].thr = kind == FD_KIND_GBT ? leaf_value[go] : 0.0;
+                if (kind != FD_KIND_GBT) {
+                    const double c0 = leaf_value[2 * (size_t)go], c1 = leaf_value[2 * (size_t)go + 1];
+                    if (kind == FD_KIND_DT) {
+                        leaf2[n] = make_double2(c0, c1);
+                    } else {  // votes(i) += classCounts(i) / total, skipped when total == 0
+                        const double tot = c0 + c1;
+                        leaf2[n] = tot != 0.0 ? make_double2(c0 / tot, c1 / tot) : make_double2(0.0, 0.0);
+                    }
+                }
+            } else {
+                if (feature[go] >= h->m.num_features && h->m.num_features > 0)
+                    return set_err(h, FD_ERR_INVALID, "tree %d node %d splits on feature %d >= numFeatures", t, o, feature[go]);
+                const int l = left[go], r = right[go];
+                if (l <= 0 || r <= 0 || l >= cnt || r >= cnt || next + 2 > base + cnt)
+                    return set_err(h, FD_ERR_INVALID, "tree %d node %d has bad children", t, o);
+                nodes[n].feat = feature[go];
+                nodes[n].thr = threshold[go];
+                nodes[n].child = next;
+                queue.push_back({l, next});
+                queue.push_back({r, next + 1});
+                next += 2;
+            }
+        }
+        if (next != base + cnt) return set_err(h, FD_ERR_INVALID, "tree %d is not a connected binary tree", t);
+    }
+    Model& m = h->m;
+    int rc = upload(h, &m.nodes, nodes.data(), nodes.size());
+    if (!rc) rc = upload(h, &m.leaf2, leaf2.data(), leaf2.size());
+    if (!rc) rc = upload(h, &m.roots, roots.data(), roots.size());
+    if (!rc && kind == FD_KIND_GBT) rc = upload(h, &m.tree_w, tree_weights, (size_t)n_trees);
+    if (rc) return rc;
+    m.kind = kind;
+    m.n_trees = n_trees;
+    m.n_classes = 2;
+    m.n_nodes = total;
+    m.classifier = 2;
+    return FD_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,138 @@
+// fd_common.cuh -- handle layout, error plumbing and small device helpers shared by the kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/fdb200.h"
+
+namespace fd {
+
+// ---- on-device model pieces -------------------------------------------------------------------
+// One decision-tree node, 16 bytes so a visit is ONE 128-bit load.  Nodes of a forest are laid out
+// breadth-first per tree with the two children of a node adjacent (right = left + 1).
+//   internal: feat >= 0, thr = split threshold, child = absolute index of the left child
+//   leaf    : feat <  0, thr = leaf prediction (GBT), child = absolute node index (row of leaf2[])
+struct __align__(16) Node {
+    double thr;
+    int32_t feat;
+    int32_t child;
+};
+
+constexpr uint32_t EMPTY_KEY = 0xFFFFFFFFu;
+
+// control block at the start of the workspace (device memory, written by kernels)
+struct Ctrl {
+    unsigned long long tmp_cursor;  // entries allocated in the CSR staging buffer
+    unsigned int big_count;         // dialogues deferred to the wide-table kernel
+    unsigned int tmp_overflow;      // staging buffer was too small
+    int status;                     // sticky device-side status (FD_OK / FD_ERR_LIMIT)
+    unsigned int pad[3];
+};
+
+struct Model {
+    // stop words: open-addressed table of 16-byte slots keyed by murmur3(word, 42)
+    uint4* sw_slots = nullptr;  // x = len (|0x80000000 when > 12 bytes), y/z/w = first 12 bytes or y = pool offset
+    int sw_cap = 0;             // power of two, 0 = no stop words
+    uint8_t* sw_pool = nullptr; // bytes of words longer than 12
+    int empty_is_stop = 0;
+    // hashing
+    int32_t num_features = 0;
+    int binary = 0;
+    uint32_t empty_idx = 0;  // bucket of the empty token
+    uint32_t mod_magic = 0;  // floor(2^32 / num_features)
+    uint32_t mod_r32 = 0;    // 2^32 mod num_features
+    int mod_pow2 = 0;
+    // idf
+    double* idf = nullptr;
+    // classifier
+    int classifier = 0;  // 0 none, 1 linear, 2 forest
+    double* coef = nullptr;
+    double intercept = 0.0, raw_threshold = 0.0;
+    int kind = 0, n_trees = 0, n_classes = 2;
+    Node* nodes = nullptr;
+    int32_t* roots = nullptr;  // absolute root index per tree
+    double2* leaf2 = nullptr;  // DT: raw class stats, RF: stats / total (0,0 when total == 0)
+    double* tree_w = nullptr;
+    int n_nodes = 0;
+};
+
+}  // namespace fd
+
+struct fd_handle {
+    int device = 0;
+    int sm_count = 148;
+    std::string err;
+    fd::Model m;
+    // workspace
+    char* ws = nullptr;
+    size_t ws_bytes = 0;
+    // featurize state between begin/finish
+    int64_t feat_rows = -1;
+    int64_t feat_nnz = 0;
+    size_t off_nnz = 0, off_tmpoff = 0, off_tmp = 0, off_bsum = 0;
+    int64_t tmp_cap = 0;
+    int64_t launches = 0;
+    // host-transform staging
+    cudaStream_t hs[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t hev[3] = {nullptr, nullptr, nullptr};
+    char* hbuf[3] = {nullptr, nullptr, nullptr};
+    size_t hbuf_bytes[3] = {0, 0, 0};
+    fd::Ctrl* pinned_ctrl = nullptr;
+};
+
+namespace fd {
+
+int set_err(fd_handle* h, int code, const char* fmt, ...);
+int cuda_fail(fd_handle* h, cudaError_t e, const char* what);
+int ensure_ws(fd_handle* h, size_t bytes);
+
+#define FD_CUDA(h, call)                                             \
+    do {                                                             \
+        cudaError_t e__ = (call);                                    \
+        if (e__ != cudaSuccess) return fd::cuda_fail(h, e__, #call); \
+    } while (0)
+
+// ---- murmur3 x86_32 pieces (host + device) ------------------------------------------------------
+__host__ __device__ __forceinline__ uint32_t rotl32(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+__host__ __device__ __forceinline__ uint32_t mm_k(uint32_t k) {
+    k *= 0xcc9e2d51u;
+    k = rotl32(k, 15);
+    return k * 0x1b873593u;
+}
+__host__ __device__ __forceinline__ uint32_t mm_h(uint32_t h, uint32_t k) {
+    h ^= k;
+    h = rotl32(h, 13);
+    return h * 5u + 0xe6546b64u;
+}
+__host__ __device__ __forceinline__ uint32_t mm_fmix(uint32_t h, uint32_t len) {
+    h ^= len;
+    h ^= h >> 16;
+    h *= 0x85ebca6bu;
+    h ^= h >> 13;
+    h *= 0xc2b2ae35u;
+    h ^= h >> 16;
+    return h;
+}
+inline uint32_t murmur3_host(const uint8_t* p, int n, uint32_t seed = 42u) {
+    uint32_t h = seed;
+    int nb = n / 4;
+    for (int i = 0; i < nb; ++i) {
+        uint32_t k = (uint32_t)p[4 * i] | ((uint32_t)p[4 * i + 1] << 8) | ((uint32_t)p[4 * i + 2] << 16) |
+                     ((uint32_t)p[4 * i + 3] << 24);
+        h = mm_h(h, mm_k(k));
+    }
+    uint32_t k = 0;
+    for (int i = 0; i < (n & 3); ++i) k |= (uint32_t)p[4 * nb + i] << (8 * i);
+    if (n & 3) h ^= mm_k(k);
+    return mm_fmix(h, (uint32_t)n);
+}
+// Utils.nonNegativeMod on the signed value of h
+inline uint32_t nonneg_mod_host(uint32_t h, int32_t nf) {
+    int32_t r = (int32_t)h % nf;
+    return (uint32_t)(r < 0 ? r + nf : r);
+}
+
+}  // namespace fd

@@ -1,0 +1,845 @@
+// fd_rows.cu -- the dialogue kernels: clean -> tokenise -> stop-word filter -> murmur3 HashingTF ->
+// per-dialogue term counts, followed by either CSR emission or a fused classifier epilogue.
+//
+// One WARP owns one dialogue at a time.  Its UTF-8 bytes are staged from HBM into the warp's shared
+// memory windows (1 KiB, double-buffered) with TMA bulk copies (cp.async.bulk + mbarrier), so the
+// next window -- of this dialogue or of the warp's next dialogue -- is in flight while the current
+// one is hashed.  Per window:
+//   pass A  each lane classifies 32 bytes with SWAR arithmetic (letter / separator / dropped),
+//           lower-cases in place, and publishes a letter bitmask, a separator bitmask and the list
+//           of token start offsets;
+//   pass B  one token per lane: MurmurHash3_x86_32(seed 42) straight out of shared memory,
+//           stop-word probe (shared-memory table keyed by the same hash), nonNegativeMod, and an
+//           atomicCAS insert into the warp's open-addressed (bucket -> count) table.
+// At the end of a dialogue the table is either compacted + bitonic-sorted and appended to the CSR
+// staging buffer (featurize), dotted with the logistic coefficients in ascending-bucket order, or
+// probed directly by a lane-per-tree walk over the 16-byte forest nodes (DT / RF / GBT).
+//
+// Semantics restated from Spark 3.5.5; reference call sites:
+// utils/agent_api.py:143-144 (cleaning), fraud_detection_spark.py:50-53 (Tokenizer, StopWordsRemover,
+// HashingTF/IDF stages), utils/agent_api.py:158-167 (transform + result columns).
+#include "fd_rows.cuh"
+
+namespace fd {
+
+// ------------------------------------------------------------------------------------------------
+// PTX helpers: mbarrier + TMA bulk copy (global -> shared), sm_90+/sm_100a
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, unsigned long long* b) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(b))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* b, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+            : "=r"(ok)
+            : "r"(smem_u32(b)), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+
+__device__ __forceinline__ uint32_t low_mask(int n) { return n >= 32 ? 0xFFFFFFFFu : ((1u << n) - 1u); }
+// gather the four 0x80 flag bits of a SWAR word into a nibble (byte 0 -> bit 0)
+__device__ __forceinline__ uint32_t movemask4(uint32_t f80) { return ((f80 >> 7) * 0x01020408u) >> 24; }
+
+// nonNegativeMod(int32(h), nf)
+__device__ __forceinline__ uint32_t feature_index(uint32_t h, const Model& m) {
+    if (m.mod_pow2) return h & (uint32_t)(m.num_features - 1);
+    const uint32_t nf = (uint32_t)m.num_features;
+    uint32_t q = __umulhi(h, m.mod_magic);
+    uint32_t r = h - q * nf;  // h mod nf, possibly + a few nf
+    while (r >= nf) r -= nf;
+    if ((int32_t)h < 0) r = (r >= m.mod_r32) ? r - m.mod_r32 : r + nf - m.mod_r32;  // value is h - 2^32
+    return r;
+}
+
+__device__ __forceinline__ uint32_t tab_slot(uint32_t idx, int log2cap) { return (idx * 0x9E3779B1u) >> (32 - log2cap); }
+
+// (bucket -> count) insert; returns true when the bucket is new for this dialogue
+__device__ __forceinline__ bool tab_insert(unsigned long long* tab, int log2cap, uint32_t idx, uint32_t inc, bool binary) {
+    const uint32_t mask = (1u << log2cap) - 1u;
+    uint32_t slot = tab_slot(idx, log2cap);
+    for (;;) {
+        unsigned int* cell = reinterpret_cast<unsigned int*>(tab + slot);  // [0] = count, [1] = key
+        unsigned int old = atomicCAS(cell + 1, EMPTY_KEY, idx);
+        if (old == EMPTY_KEY || old == idx) {
+            if (binary)
+                cell[0] = 1u;
+            else
+                atomicAdd(cell, inc);
+            return old == EMPTY_KEY;
+        }
+        slot = (slot + 1u) & mask;
+    }
+}
+
+__device__ __forceinline__ uint32_t tab_lookup(const unsigned long long* tab, int log2cap, uint32_t idx) {
+    const uint32_t mask = (1u << log2cap) - 1u;
+    uint32_t slot = tab_slot(idx, log2cap);
+    for (;;) {
+        unsigned long long e = tab[slot];
+        uint32_t k = (uint32_t)(e >> 32);
+        if (k == idx) return (uint32_t)e;
+        if (k == EMPTY_KEY) return 0u;
+        slot = (slot + 1u) & mask;
+    }
+}
+
+// resumable murmur3 state for tokens whose kept bytes are not contiguous (or span windows)
+struct HashState {
+    uint32_t h, k, n, b0, b1, b2;
+    __device__ __forceinline__ void reset() {
+        h = 42u;
+        k = 0u;
+        n = 0u;
+        b0 = b1 = b2 = 0u;
+    }
+    __device__ __forceinline__ void put(uint32_t c) {
+        k |= c << (8u * (n & 3u));
+        if ((n & 3u) == 3u) {
+            if (n < 4u) b0 = k;
+            else if (n < 8u) b1 = k;
+            else if (n < 12u) b2 = k;
+            h = mm_h(h, mm_k(k));
+            k = 0u;
+        }
+        ++n;
+    }
+    __device__ __forceinline__ uint32_t finish() {
+        uint32_t hh = h;
+        if (n & 3u) {
+            if (n < 4u) b0 = k;
+            else if (n < 8u) b1 = k;
+            else if (n < 12u) b2 = k;
+            hh ^= mm_k(k);
+        }
+        return mm_fmix(hh, n);
+    }
+};
+
+__device__ __forceinline__ bool letter_at(const uint32_t* lmask, int p) { return (lmask[p >> 5] >> (p & 31)) & 1u; }
+
+// is the token (hash h, n kept bytes, first 12 bytes b0..b2) a stop word?
+// long words (> 12 bytes) are compared byte by byte against the pool, walking the token's kept bytes.
+__device__ bool is_stop_word(const uint4* sw, int sw_cap, const uint8_t* pool, uint32_t h, uint32_t n, uint32_t b0,
+                             uint32_t b1, uint32_t b2, const uint8_t* rb, const uint32_t* lmask, int s, int e) {
+    const uint32_t mask = (uint32_t)sw_cap - 1u;
+    uint32_t slot = h & mask;
+    for (;;) {
+        const uint4 w = sw[slot];
+        if (w.x == 0xFFFFFFFFu) return false;
+        if ((w.x & 0x7FFFFFFFu) == n) {
+            if (!(w.x & 0x80000000u)) {
+                if (w.y == b0 && w.z == b1 && w.w == b2) return true;
+            } else if (s >= 0) {
+                const uint8_t* word = pool + w.y;
+                uint32_t i = 0;
+                bool same = true;
+                for (int p = s; p < e && same; ++p)
+                    if (letter_at(lmask, p)) same = (rb[p] == word[i++]);
+                if (same) return true;
+            }
+        }
+        slot = (slot + 1u) & mask;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// the kernel
+// ------------------------------------------------------------------------------------------------
+template <int MODE, bool CLEAN, bool BIG>
+__global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS) k_rows(const RowArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint4* sw = reinterpret_cast<uint4*>(smem_raw);
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const Model& m = a.m;
+    WarpSmem& S = *reinterpret_cast<WarpSmem*>(smem_raw + (size_t)m.sw_cap * 16 + (size_t)warp * sizeof(WarpSmem));
+
+    for (int i = threadIdx.x; i < m.sw_cap; i += blockDim.x) sw[i] = m.sw_slots[i];
+    if (lane == 0) {
+        mbar_init(&S.mbar[0], 1);
+        mbar_init(&S.mbar[1], 1);
+        fence_mbar_init();
+    }
+    if (lane < 4) S.lmask[32 + lane] = 0u;
+
+    unsigned long long* tab = BIG ? a.big_tabs + ((size_t)blockIdx.x << BIG_LOG2) : S.tab;
+    constexpr int TLOG2 = BIG ? BIG_LOG2 : TAB_LOG2;
+    constexpr int TCAP = 1 << TLOG2;
+    const long long n_items = BIG ? (long long)a.ctrl->big_count : a.n_rows;
+    const long long stride = BIG ? (long long)gridDim.x : (long long)gridDim.x * ROW_WARPS;
+    long long item = BIG ? (long long)blockIdx.x : (long long)blockIdx.x * ROW_WARPS + warp;
+    if (BIG && item >= n_items) return;  // nothing deferred: do not touch the wide table
+    {
+        uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);  // count = 0, key = EMPTY
+        for (int i = lane; i < TCAP / 2; i += 32) reinterpret_cast<uint4*>(tab)[i] = ff;
+    }
+    __syncthreads();
+    if (item >= n_items) return;
+
+    const uint8_t* text = a.text;
+    const bool binary = m.binary != 0;
+
+    // ---- window bookkeeping (all warp-uniform) ----
+    long long row = BIG ? a.big_rows[item] : item;
+    long long row_beg = a.offs[row], row_end = a.offs[row + 1];
+    long long wbase = row_beg & ~15LL;             // global byte offset of buffer byte 0
+    int lo = (int)(row_beg - wbase);               // first valid byte of the window
+    int hi = (int)min((long long)ROW_CH, row_end - wbase);
+    bool last = (row_end - wbase) <= ROW_CH;
+    int lbmin = lo;                                // lowest buffer offset a UTF-8 look-back may read
+    int buf = 0;
+    uint32_t phase0 = 0, phase1 = 0;
+    if (lane == 0) {
+        uint32_t bytes = (uint32_t)((hi + 15) & ~15);
+        if (bytes) {
+            mbar_expect_tx(&S.mbar[0], bytes);
+            tma_load_1d(S.raw[0], text + wbase, bytes, &S.mbar[0]);
+        }
+    }
+    bool cur_loaded = hi > 0;
+
+    // ---- per-dialogue state ----
+    uint32_t D = 0;        // distinct buckets so far
+    uint32_t pend = 0;     // empty tokens not yet known to be interior
+    uint32_t row_sp = 0;   // separators seen
+    bool row_letter = false;
+    bool big = false;      // deferred to the wide-table kernel (or over the limit there)
+    bool gt_active = false;  // first token of the window continues a token from the previous window
+    HashState gt;            // its state (lane 0 only)
+    gt.reset();
+
+    for (;;) {
+        uint8_t* rb = S.raw[buf];
+        if (cur_loaded) {
+            if (buf == 0) {
+                mbar_wait(&S.mbar[0], phase0);
+                phase0 ^= 1u;
+            } else {
+                mbar_wait(&S.mbar[1], phase1);
+                phase1 ^= 1u;
+            }
+        }
+
+        // ================= pass A: classify 32 bytes per lane =================
+        uint32_t L = 0, SP = 0;
+        {
+            uint4 q0 = *reinterpret_cast<const uint4*>(rb + 32 * lane);
+            uint4 q1 = *reinterpret_cast<const uint4*>(rb + 32 * lane + 16);
+            uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+            const int lo_l = min(max(lo - 32 * lane, 0), 32), hi_l = min(max(hi - 32 * lane, 0), 32);
+            const uint32_t vmask = hi_l > lo_l ? (low_mask(hi_l) & ~low_mask(lo_l)) : 0u;
+            uint32_t H = 0;
+            bool changed = false;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t x = w[j];
+                uint32_t l80, s80, nx;
+                if (CLEAN) {
+                    const uint32_t v7 = (x | 0x20202020u) & 0x7F7F7F7Fu;
+                    const uint32_t ge_a = v7 + 0x1F1F1F1Fu;  // bit7 <=> byte >= 0x61
+                    const uint32_t gt_z = v7 + 0x05050505u;  // bit7 <=> byte >= 0x7B
+                    l80 = ge_a & ~gt_z & ~x & 0x80808080u;
+                    const uint32_t z = x ^ 0x20202020u;
+                    s80 = ~(((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z) & 0x80808080u;
+                    nx = x | (l80 >> 2);
+                    H |= x & 0x80808080u;
+                } else {
+                    const uint32_t t = x & 0x7F7F7F7Fu;
+                    const uint32_t ge9 = t + 0x77777777u;   // >= 0x09
+                    const uint32_t geE = t + 0x72727272u;   // >= 0x0E
+                    const uint32_t z = x ^ 0x20202020u;
+                    const uint32_t sp = ~(((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z) & 0x80808080u;
+                    s80 = ((ge9 & ~geE & ~x) | sp) & 0x80808080u;
+                    l80 = ~s80 & 0x80808080u;
+                    const uint32_t geA = t + 0x3F3F3F3Fu;   // >= 'A'
+                    const uint32_t gtZ = t + 0x25252525u;   // >= '['
+                    const uint32_t up80 = geA & ~gtZ & ~x & 0x80808080u;
+                    nx = x | (up80 >> 2);
+                }
+                L |= movemask4(l80) << (4 * j);
+                SP |= movemask4(s80) << (4 * j);
+                changed |= (nx != x);
+                w[j] = nx;
+            }
+            L &= vmask;
+            SP &= vmask;
+            if (changed) {
+                *reinterpret_cast<uint4*>(rb + 32 * lane) = make_uint4(w[0], w[1], w[2], w[3]);
+                *reinterpret_cast<uint4*>(rb + 32 * lane + 16) = make_uint4(w[4], w[5], w[6], w[7]);
+            }
+            if (CLEAN && H) {
+                // U+0130 (C4 B0) -> 'i', U+212A (E2 84 AA) -> 'k': their lower-case forms keep an ASCII letter
+                for (int j = 0; j < 32; ++j) {
+                    const int p = 32 * lane + j;
+                    if (!((vmask >> j) & 1u)) continue;
+                    const uint8_t c = rb[p];
+                    if (c == 0xB0 && p - 1 >= lbmin && rb[p - 1] == 0xC4) {
+                        rb[p] = 'i';
+                        L |= 1u << j;
+                    } else if (c == 0xAA && p - 2 >= lbmin && rb[p - 1] == 0x84 && rb[p - 2] == 0xE2) {
+                        rb[p] = 'k';
+                        L |= 1u << j;
+                    }
+                }
+            }
+        }
+        S.lmask[lane] = L;
+        // token starts: one after every separator
+        const int nsp = __popc(SP);
+        int incl = nsp;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if (lane >= d) incl += v;
+        }
+        const int win_sp = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        {
+            int base = 1 + incl - nsp;
+            uint32_t sp = SP;
+            while (sp) {
+                const int b = __ffs(sp) - 1;
+                sp &= sp - 1u;
+                S.tok[base++] = (uint16_t)(32 * lane + b + 1);
+            }
+        }
+        const int T = win_sp + 1;
+        if (lane == 0) {
+            S.tok[0] = (uint16_t)lo;
+            S.tok[T] = (uint16_t)(hi + 1);
+        }
+        const int my_ll = L ? (32 * lane + 31 - __clz(L)) : -1;
+        const int last_letter = __reduce_max_sync(0xFFFFFFFFu, my_ll);
+        __syncwarp();
+
+        // ================= choose + prefetch the next window =================
+        // tokens complete in this window: all of them when it is the dialogue's last window, otherwise
+        // all but the trailing one (which restarts the next window; a window without any separator is a
+        // "giant" token that is carried as hash state instead).
+        const bool giant = !last && T == 1;
+        const int Tc = last ? T : T - 1;
+        long long n_item = item, n_row = row, n_beg = row_beg, n_end = row_end, n_wbase;
+        int n_lo, n_hi, n_lbmin;
+        bool n_last, have_next = true;
+        if (!last) {
+            long long cursor = giant ? wbase + hi : wbase + (long long)S.tok[T - 1];
+            n_wbase = (cursor & ~15LL) - (giant ? 16 : 0);
+            n_lo = (int)(cursor - n_wbase);
+            n_lbmin = 0;
+        } else {
+            n_item = item + stride;
+            have_next = n_item < n_items;
+            if (have_next) {
+                n_row = BIG ? a.big_rows[n_item] : n_item;
+                n_beg = a.offs[n_row];
+                n_end = a.offs[n_row + 1];
+            }
+            n_wbase = n_beg & ~15LL;
+            n_lo = (int)(n_beg - n_wbase);
+            n_lbmin = n_lo;
+        }
+        n_hi = (int)min((long long)ROW_CH, n_end - n_wbase);
+        n_last = (n_end - n_wbase) <= ROW_CH;
+        const bool n_loaded = have_next && n_hi > 0;
+        if (n_loaded && lane == 0) {
+            const uint32_t bytes = (uint32_t)((n_hi + 15) & ~15);
+            fence_proxy_async();
+            mbar_expect_tx(&S.mbar[buf ^ 1], bytes);
+            tma_load_1d(S.raw[buf ^ 1], text + n_wbase, bytes, &S.mbar[buf ^ 1]);
+        }
+
+        // ================= pass B: one token per lane =================
+        row_sp += (uint32_t)win_sp;
+        if (last_letter >= 0) {
+            // a letter exists in this window: empties carried from earlier windows were interior
+            if (pend && !big && !m.empty_is_stop) {
+                bool isnew = false;
+                if (lane == 0) isnew = tab_insert(tab, TLOG2, m.empty_idx, pend, binary);
+                D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
+            }
+            pend = 0;
+            row_letter = true;
+        }
+        if (!big) {
+            if (giant || gt_active) {
+                // token 0 of this window continues / starts a multi-window token: lane 0 feeds it serially
+                const int s0 = S.tok[0], e0 = giant ? hi : (int)S.tok[1] - 1;
+                if (lane == 0)
+                    for (int p = s0; p < e0; ++p)
+                        if (letter_at(S.lmask, p)) gt.put(rb[p]);
+                if (!giant) {  // it ends here (separator or end of dialogue)
+                    bool isnew = false, was_empty = false;
+                    if (lane == 0) {
+                        const uint32_t h = gt.finish();
+                        if (gt.n == 0) {
+                            was_empty = true;
+                        } else if (!(m.sw_cap && is_stop_word(sw, m.sw_cap, m.sw_pool, h, gt.n, gt.b0, gt.b1, gt.b2, rb,
+                                                              S.lmask, -1, -1))) {
+                            isnew = tab_insert(tab, TLOG2, feature_index(h, m), 1u, binary);
+                        }
+                        gt.reset();
+                    }
+                    D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
+                    was_empty = __shfl_sync(0xFFFFFFFFu, (int)was_empty, 0);
+                    if (was_empty) {
+                        // empty multi-window token: interior iff a letter follows in this window
+                        if (S.tok[0] <= last_letter) {
+                            bool nw2 = false;
+                            if (lane == 0 && !m.empty_is_stop) nw2 = tab_insert(tab, TLOG2, m.empty_idx, 1u, binary);
+                            D += __popc(__ballot_sync(0xFFFFFFFFu, nw2));
+                        } else {
+                            pend += 1;
+                        }
+                    }
+                }
+            }
+            const int t_first = (giant || gt_active) ? 1 : 0;
+            for (int t0 = t_first; t0 < Tc; t0 += 32) {
+                if (D + 32u > (uint32_t)(TCAP - TCAP / 4)) {  // keep the table at most 3/4 full
+                    big = true;
+                    break;
+                }
+                const int t = t0 + lane;
+                bool isnew = false;
+                bool pending_empty = false;
+                if (t < Tc) {
+                    const int s = S.tok[t], e = (int)S.tok[t + 1] - 1;
+                    const int len = e - s;
+                    uint32_t h = 42u, n = 0, b0 = 0, b1 = 0, b2 = 0;
+                    bool fast = false, empty = false;
+                    int f = 0;
+                    if (len <= 32) {
+                        const int wi = s >> 5, sh = s & 31;
+                        const uint32_t win = __funnelshift_r(S.lmask[wi], S.lmask[wi + 1], sh);
+                        const uint32_t bits = win & low_mask(len);
+                        if (bits == 0u) {
+                            empty = true;
+                        } else {
+                            f = __ffs(bits) - 1;
+                            n = (uint32_t)__popc(bits);
+                            fast = (bits >> f) == low_mask((int)n);
+                        }
+                    }
+                    if (fast) {
+                        const int p0 = s + f;
+                        const uint32_t* wp = reinterpret_cast<const uint32_t*>(rb + (p0 & ~3));
+                        const int sh = (p0 & 3) * 8;
+                        uint32_t prev = wp[0];
+                        const int nb = (int)(n >> 2);
+                        for (int i = 0; i < nb; ++i) {
+                            const uint32_t nxt = wp[i + 1];
+                            const uint32_t k = __funnelshift_r(prev, nxt, sh);
+                            prev = nxt;
+                            if (i == 0) b0 = k;
+                            else if (i == 1) b1 = k;
+                            else if (i == 2) b2 = k;
+                            h = mm_h(h, mm_k(k));
+                        }
+                        const int tail = (int)(n & 3u);
+                        if (tail) {
+                            const uint32_t nxt = wp[nb + 1];
+                            const uint32_t k = __funnelshift_r(prev, nxt, sh) & low_mask(8 * tail);
+                            if (nb == 0) b0 = k;
+                            else if (nb == 1) b1 = k;
+                            else if (nb == 2) b2 = k;
+                            h ^= mm_k(k);
+                        }
+                        h = mm_fmix(h, n);
+                    } else if (!empty) {
+                        HashState hs;
+                        hs.reset();
+                        for (int p = s; p < e; ++p)
+                            if (letter_at(S.lmask, p)) hs.put(rb[p]);
+                        h = hs.finish();
+                        n = hs.n;
+                        b0 = hs.b0;
+                        b1 = hs.b1;
+                        b2 = hs.b2;
+                        empty = (n == 0u);
+                    }
+                    if (empty) {
+                        if (s <= last_letter) {
+                            if (!m.empty_is_stop) isnew = tab_insert(tab, TLOG2, m.empty_idx, 1u, binary);
+                        } else {
+                            pending_empty = true;
+                        }
+                    } else if (!(m.sw_cap && is_stop_word(sw, m.sw_cap, m.sw_pool, h, n, b0, b1, b2, rb, S.lmask, s, e))) {
+                        isnew = tab_insert(tab, TLOG2, feature_index(h, m), 1u, binary);
+                    }
+                }
+                D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
+                pend += __popc(__ballot_sync(0xFFFFFFFFu, pending_empty));
+            }
+        }
+        gt_active = giant;
+        __syncwarp();
+
+        // ================= end of dialogue =================
+        if (last) {
+            if (!big && row_sp == 0 && !row_letter && !m.empty_is_stop) {
+                // no separator anywhere and nothing kept: Java's split returns [""] -- one empty token
+                bool isnew = false;
+                if (lane == 0) isnew = tab_insert(tab, TLOG2, m.empty_idx, 1u, binary);
+                D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
+            }
+            __syncwarp();
+            if (big) {
+                if (BIG) {
+                    if (lane == 0) a.ctrl->status = FD_ERR_LIMIT;
+                } else if (lane == 0) {
+                    const unsigned int pos = atomicAdd(&a.ctrl->big_count, 1u);
+                    if ((long long)pos < a.big_cap) a.big_rows[pos] = row;
+                    else a.ctrl->status = FD_ERR_LIMIT;
+                }
+            } else {
+                row_epilogue<MODE>(a, S, tab, TLOG2, row, (int)D, lane);
+            }
+            // reset the table and the per-dialogue state
+            __syncwarp();
+            {
+                uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);  // count = 0, key = EMPTY
+                for (int i = lane; i < TCAP / 2; i += 32) reinterpret_cast<uint4*>(tab)[i] = ff;
+            }
+            D = 0;
+            pend = 0;
+            row_sp = 0;
+            row_letter = false;
+            big = false;
+            gt_active = false;
+            if (lane == 0) gt.reset();
+            __syncwarp();
+        }
+        if (!have_next) break;
+        item = n_item;
+        row = n_row;
+        row_beg = n_beg;
+        row_end = n_end;
+        wbase = n_wbase;
+        lo = n_lo;
+        hi = n_hi;
+        last = n_last;
+        lbmin = n_lbmin;
+        cur_loaded = n_loaded;
+        buf ^= 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// end-of-dialogue epilogues
+// ------------------------------------------------------------------------------------------------
+// compact the table in place to entries [0, n) and bitonic-sort them ascending by bucket
+__device__ int compact_and_sort(unsigned long long* tab, int log2cap, int lane) {
+    const int cap = 1 << log2cap;
+    int w = 0;
+    for (int base = 0; base < cap; base += 32) {
+        const unsigned long long e = tab[base + lane];
+        const bool v = (uint32_t)(e >> 32) != EMPTY_KEY;
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, v);
+        __syncwarp();
+        if (v) tab[w + __popc(bal & ((1u << lane) - 1u))] = e;
+        w += __popc(bal);
+        __syncwarp();
+    }
+    const int n = w;
+    int P = 1;
+    while (P < n) P <<= 1;
+    for (int i = n + lane; i < P; i += 32) tab[i] = ~0ULL;
+    __syncwarp();
+    for (int k = 2; k <= P; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int c = lane; c < (P >> 1); c += 32) {
+                const int i = ((c & ~(j - 1)) << 1) | (c & (j - 1));
+                const int ixj = i | j;
+                const unsigned long long x = tab[i], y = tab[ixj];
+                const bool asc = (i & k) == 0;
+                if ((x > y) == asc) {
+                    tab[i] = y;
+                    tab[ixj] = x;
+                }
+            }
+            __syncwarp();
+        }
+    }
+    return n;
+}
+
+__device__ __forceinline__ double feat_value(const Model& m, uint32_t idx, uint32_t cnt) {
+    const double c = (double)cnt;
+    return m.idf ? __dmul_rn(c, __ldg(m.idf + idx)) : c;
+}
+
+__device__ __forceinline__ void write_result(const RowArgs& a, long long row, int lane, double pred, double p0, double p1,
+                                             double r0, double r1) {
+    if (lane == 0) a.pred[row] = pred;
+    else if (lane == 1) a.prob[2 * row] = p0;
+    else if (lane == 2) a.prob[2 * row + 1] = p1;
+    else if (lane == 3) a.raw[2 * row] = r0;
+    else if (lane == 4) a.raw[2 * row + 1] = r1;
+}
+
+// walk one tree with the dialogue's (bucket -> count) table; returns the absolute leaf index
+__device__ __forceinline__ int walk_tree(const Model& m, const unsigned long long* tab, int log2cap, int root, Node& leaf) {
+    int n = root;
+    for (;;) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(m.nodes + n));
+        Node nd;
+        nd.thr = __hiloint2double((int)q.y, (int)q.x);
+        nd.feat = (int)q.z;
+        nd.child = (int)q.w;
+        if (nd.feat < 0) {
+            leaf = nd;
+            return n;
+        }
+        const uint32_t cnt = tab_lookup(tab, log2cap, (uint32_t)nd.feat);
+        const double x = cnt ? feat_value(m, (uint32_t)nd.feat, cnt) : 0.0;
+        n = nd.child + ((x <= nd.thr) ? 0 : 1);
+    }
+}
+
+template <int MODE>
+__device__ void row_epilogue(const RowArgs& a, WarpSmem& S, unsigned long long* tab, int log2cap, long long row, int D,
+                             int lane) {
+    const Model& m = a.m;
+    double* scratch = reinterpret_cast<double*>(S.tok);  // 64 doubles of warp scratch (tok is free now)
+    if (MODE == MODE_CSR) {
+        D = compact_and_sort(tab, log2cap, lane);
+        unsigned long long pos = 0;
+        if (lane == 0) pos = atomicAdd(&a.ctrl->tmp_cursor, (unsigned long long)D);
+        pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+        if ((long long)(pos + D) <= a.tmp_cap) {
+            for (int i = lane; i < D; i += 32) a.tmp[pos + i] = tab[i];
+        } else if (lane == 0) {
+            a.ctrl->tmp_overflow = 1u;
+        }
+        if (lane == 0) {
+            a.row_nnz[row] = D;
+            a.row_tmpoff[row] = (long long)pos;
+        }
+    } else if (MODE == MODE_LINEAR) {
+        D = compact_and_sort(tab, log2cap, lane);
+        double sum = 0.0;
+        for (int b = 0; b < D; b += 32) {
+            const int i = b + lane;
+            if (i < D) {
+                const unsigned long long e = tab[i];
+                const uint32_t idx = (uint32_t)(e >> 32);
+                scratch[lane] = __dmul_rn(feat_value(m, idx, (uint32_t)e), __ldg(m.coef + idx));
+            }
+            __syncwarp();
+            if (lane == 0) {
+                const int cnt = min(32, D - b);
+                for (int l = 0; l < cnt; ++l) sum = __dadd_rn(sum, scratch[l]);
+            }
+            __syncwarp();
+        }
+        sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
+        const double mg = __dadd_rn(sum, m.intercept);
+        const double p0 = 1.0 / (1.0 + exp(mg));
+        write_result(a, row, lane, mg > m.raw_threshold ? 1.0 : 0.0, p0, 1.0 - p0, -mg, mg);
+    } else if (MODE == MODE_DT) {
+        Node leaf;
+        const int n = walk_tree(m, tab, log2cap, __ldg(m.roots), leaf);
+        const double2 st = __ldg(m.leaf2 + n);
+        const double tot = __dadd_rn(st.x, st.y);
+        const double p0 = tot != 0.0 ? st.x / tot : st.x, p1 = tot != 0.0 ? st.y / tot : st.y;
+        write_result(a, row, lane, st.y > st.x ? 1.0 : 0.0, p0, p1, st.x, st.y);
+    } else if (MODE == MODE_RF) {
+        double v = 0.0;  // lane 0: class 0 votes, lane 1: class 1 votes
+        for (int b = 0; b < m.n_trees; b += 32) {
+            const int t = b + lane;
+            if (t < m.n_trees) {
+                Node leaf;
+                const int n = walk_tree(m, tab, log2cap, __ldg(m.roots + t), leaf);
+                const double2 st = __ldg(m.leaf2 + n);
+                scratch[lane] = st.x;
+                scratch[32 + lane] = st.y;
+            }
+            __syncwarp();
+            if (lane < 2) {
+                const int cnt = min(32, m.n_trees - b);
+                const double* src = scratch + 32 * lane;
+                for (int l = 0; l < cnt; ++l) v = __dadd_rn(v, src[l]);
+            }
+            __syncwarp();
+        }
+        const double v0 = __shfl_sync(0xFFFFFFFFu, v, 0), v1 = __shfl_sync(0xFFFFFFFFu, v, 1);
+        const double tot = __dadd_rn(v0, v1);
+        const double p0 = tot != 0.0 ? v0 / tot : v0, p1 = tot != 0.0 ? v1 / tot : v1;
+        write_result(a, row, lane, v1 > v0 ? 1.0 : 0.0, p0, p1, v0, v1);
+    } else if (MODE == MODE_GBT) {
+        double mg = 0.0;
+        for (int b = 0; b < m.n_trees; b += 32) {
+            const int t = b + lane;
+            if (t < m.n_trees) {
+                Node leaf;
+                walk_tree(m, tab, log2cap, __ldg(m.roots + t), leaf);
+                scratch[lane] = __dmul_rn(leaf.thr, __ldg(m.tree_w + t));
+            }
+            __syncwarp();
+            if (lane == 0) {
+                const int cnt = min(32, m.n_trees - b);
+                for (int l = 0; l < cnt; ++l) mg = __dadd_rn(mg, scratch[l]);
+            }
+            __syncwarp();
+        }
+        mg = __shfl_sync(0xFFFFFFFFu, mg, 0);
+        const double r0 = -mg;
+        const double p0 = 1.0 / (1.0 + exp(-2.0 * r0));
+        write_result(a, row, lane, mg > r0 ? 1.0 : 0.0, p0, 1.0 - p0, r0, mg);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// CSR assembly: exclusive scan of per-dialogue nnz, then gather staging -> (idx, tf * idf)
+// ------------------------------------------------------------------------------------------------
+constexpr int SCAN_BLOCK = 1024;
+
+__global__ void k_scan_block_sums(const int32_t* __restrict__ nnz, long long n, long long* __restrict__ bsum) {
+    __shared__ long long sh[32];
+    const long long i = (long long)blockIdx.x * SCAN_BLOCK + threadIdx.x;
+    long long v = i < n ? nnz[i] : 0;
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, d);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        v = sh[threadIdx.x];
+        for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, d);
+        if (threadIdx.x == 0) bsum[blockIdx.x] = v;
+    }
+}
+
+// single block: exclusive scan of the block sums in place; total goes to bsum[n_blocks]
+__global__ void k_scan_top(long long* __restrict__ bsum, int n_blocks) {
+    __shared__ long long sh[SCAN_BLOCK];
+    __shared__ long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n_blocks; base += SCAN_BLOCK) {
+        const int i = base + threadIdx.x;
+        const long long v = i < n_blocks ? bsum[i] : 0;
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int d = 1; d < SCAN_BLOCK; d <<= 1) {
+            long long t = threadIdx.x >= d ? sh[threadIdx.x - d] : 0;
+            __syncthreads();
+            sh[threadIdx.x] += t;
+            __syncthreads();
+        }
+        if (i < n_blocks) bsum[i] = carry + sh[threadIdx.x] - v;
+        __syncthreads();
+        if (threadIdx.x == 0) carry += sh[SCAN_BLOCK - 1];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) bsum[n_blocks] = carry;
+}
+
+__global__ void k_scan_rowptr(const int32_t* __restrict__ nnz, long long n, const long long* __restrict__ bsum,
+                              long long* __restrict__ rowptr) {
+    __shared__ long long sh[SCAN_BLOCK];
+    const long long i = (long long)blockIdx.x * SCAN_BLOCK + threadIdx.x;
+    const long long v = i < n ? nnz[i] : 0;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int d = 1; d < SCAN_BLOCK; d <<= 1) {
+        long long t = threadIdx.x >= d ? sh[threadIdx.x - d] : 0;
+        __syncthreads();
+        sh[threadIdx.x] += t;
+        __syncthreads();
+    }
+    if (i < n) rowptr[i] = bsum[blockIdx.x] + sh[threadIdx.x] - v;
+    if (i == n - 1) rowptr[n] = bsum[blockIdx.x] + sh[threadIdx.x];
+}
+
+__global__ void k_gather_csr(const unsigned long long* __restrict__ tmp, const long long* __restrict__ tmpoff,
+                             const long long* __restrict__ rowptr, long long n_rows, const double* __restrict__ idf,
+                             int32_t* __restrict__ out_idx, double* __restrict__ out_val) {
+    const int lane = threadIdx.x & 31;
+    const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+    for (long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n_rows; r += nwarps) {
+        const long long o = rowptr[r], n = rowptr[r + 1] - o, t = tmpoff[r];
+        for (long long i = lane; i < n; i += 32) {
+            const unsigned long long e = tmp[t + i];
+            const uint32_t idx = (uint32_t)(e >> 32);
+            const double c = (double)(uint32_t)e;
+            out_idx[o + i] = (int32_t)idx;
+            out_val[o + i] = idf ? __dmul_rn(c, __ldg(idf + idx)) : c;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+template <int MODE, bool CLEAN>
+static cudaError_t launch_mode(fd_handle* h, const RowArgs& a, cudaStream_t st) {
+    const size_t smem = (size_t)a.m.sw_cap * 16 + (size_t)ROW_WARPS * sizeof(WarpSmem);
+    const size_t smem_big = (size_t)a.m.sw_cap * 16 + sizeof(WarpSmem);
+    auto kern = k_rows<MODE, CLEAN, false>;
+    auto kbig = k_rows<MODE, CLEAN, true>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kbig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_big);
+    if (e != cudaSuccess) return e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, ROW_THREADS, smem);
+    if (e != cudaSuccess) return e;
+    if (occ < 1) occ = 1;
+    long long want = (a.n_rows + ROW_WARPS - 1) / ROW_WARPS;
+    long long grid = (long long)h->sm_count * occ;
+    if (want < grid) grid = want;
+    if (grid < 1) grid = 1;
+    kern<<<(unsigned)grid, ROW_THREADS, smem, st>>>(a);
+    kbig<<<BIG_WORKERS, 32, smem_big, st>>>(a);
+    h->launches += 2;
+    return cudaGetLastError();
+}
+
+template <int MODE>
+static cudaError_t launch_clean(fd_handle* h, const RowArgs& a, cudaStream_t st) {
+    return (a.flags & FD_FLAG_CLEAN) ? launch_mode<MODE, true>(h, a, st) : launch_mode<MODE, false>(h, a, st);
+}
+
+cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st) {
+    switch (mode) {
+        case MODE_CSR: return launch_clean<MODE_CSR>(h, a, st);
+        case MODE_LINEAR: return launch_clean<MODE_LINEAR>(h, a, st);
+        case MODE_DT: return launch_clean<MODE_DT>(h, a, st);
+        case MODE_RF: return launch_clean<MODE_RF>(h, a, st);
+        case MODE_GBT: return launch_clean<MODE_GBT>(h, a, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, const unsigned long long* tmp,
+                                long long n_rows, long long* bsum, long long* rowptr, int32_t* out_idx, double* out_val,
+                                bool scan_only, cudaStream_t st) {
+    const int nb = (int)((n_rows + SCAN_BLOCK - 1) / SCAN_BLOCK);
+    if (scan_only) {
+        k_scan_block_sums<<<nb, SCAN_BLOCK, 0, st>>>(nnz, n_rows, bsum);
+        k_scan_top<<<1, SCAN_BLOCK, 0, st>>>(bsum, nb);
+        h->launches += 2;
+        return cudaGetLastError();
+    }
+    k_scan_rowptr<<<nb, SCAN_BLOCK, 0, st>>>(nnz, n_rows, bsum, rowptr);
+    long long g = (n_rows + 7) / 8;
+    if (g > (long long)h->sm_count * 16) g = (long long)h->sm_count * 16;
+    k_gather_csr<<<(unsigned)g, 256, 0, st>>>(tmp, tmpoff, rowptr, n_rows, h->m.idf, out_idx, out_val);
+    h->launches += 2;
+    return cudaGetLastError();
+}
+
+}  // namespace fd

@@ -1,0 +1,58 @@
+// fd_rows.cuh -- shared declarations of the dialogue kernels (fd_rows.cu) and their launchers.
+#pragma once
+#include "fd_common.cuh"
+
+namespace fd {
+
+constexpr int ROW_WARPS = 8;                 // dialogues in flight per CTA
+constexpr int ROW_THREADS = ROW_WARPS * 32;
+constexpr int ROW_CH = 1024;                 // bytes per staged window
+constexpr int ROW_RAWBUF = ROW_CH + 16;      // + slack for word over-reads at the end
+constexpr int TAB_LOG2 = 9;                  // per-warp (bucket -> count) table: 512 slots in shared memory
+constexpr int BIG_LOG2 = 18;                 // wide table (global memory) for dialogues that overflow it
+constexpr int BIG_WORKERS = 16;              // CTAs (one warp each) of the wide-table kernel
+
+enum Mode { MODE_CSR = 0, MODE_LINEAR = 1, MODE_DT = 2, MODE_RF = 3, MODE_GBT = 4 };
+
+struct __align__(16) WarpSmem {
+    uint8_t raw[2][ROW_RAWBUF];        // TMA-staged windows (double-buffered)
+    uint32_t lmask[36];                // letter bitmask of the current window (+ zero tail)
+    uint16_t tok[ROW_CH + 8];          // token start offsets of the current window; epilogue scratch
+    unsigned long long mbar[2];        // one mbarrier per window buffer
+    unsigned long long tab[1 << TAB_LOG2];  // count in the low word, bucket in the high word
+};
+static_assert(sizeof(WarpSmem) % 16 == 0, "WarpSmem must keep 16-byte alignment");
+
+struct RowArgs {
+    const uint8_t* text;
+    const int64_t* offs;
+    long long n_rows;
+    uint32_t flags;
+    Model m;
+    Ctrl* ctrl;
+    long long* big_rows;
+    long long big_cap;
+    unsigned long long* big_tabs;
+    // featurize outputs (staging)
+    int32_t* row_nnz;
+    long long* row_tmpoff;
+    unsigned long long* tmp;
+    long long tmp_cap;
+    // score outputs
+    double* pred;
+    double* prob;
+    double* raw;
+};
+
+template <int MODE>
+__device__ void row_epilogue(const RowArgs& a, WarpSmem& S, unsigned long long* tab, int log2cap, long long row, int D,
+                             int lane);
+
+cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st);
+cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, const unsigned long long* tmp,
+                                long long n_rows, long long* bsum, long long* rowptr, int32_t* out_idx, double* out_val,
+                                bool scan_only, cudaStream_t st);
+cudaError_t launch_score_csr(fd_handle* h, const int64_t* rowptr, const int32_t* idx, const double* val, long long n_rows,
+                             double* pred, double* prob, double* raw, cudaStream_t st);
+
+}  // namespace fd

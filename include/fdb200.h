@@ -1,0 +1,173 @@
+/*
+ * fdb200.h -- C-ABI of libfdb200.so: the B200 (sm_100a) hot path behind a Spark ML PipelineModel.
+ *
+ * The reference (wangwang2111/fraud-detection-spark-kafka-llm) has NO C/FFI interface of its own for
+ * this path: it calls pyspark.ml (third-party, JVM) -- PipelineModel.load (utils/agent_api.py:129),
+ * model.transform (utils/agent_api.py:158, fraud_detection_spark.py:98), Pipeline.fit
+ * (fraud_detection_spark.py:85-91).  Each entry point below therefore cites the reference call
+ * site / Spark stage whose work it replaces.  Host code stays Python and binds these with ctypes
+ * (see INTEGRATION.md); no torch types appear in any signature.
+ *
+ * Conventions
+ *  - every function returns int: 0 = FD_OK, < 0 = error code; fd_last_error(h) gives the text
+ *    (per handle, valid until the next call on that handle).
+ *  - "dev" pointers are device memory owned by the caller (e.g. a torch tensor's data_ptr()),
+ *    "host" pointers are host memory.  The library never frees or keeps caller buffers past the
+ *    completion of the stream work it enqueued.
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Compute calls are
+ *    asynchronous on that stream unless stated otherwise.
+ *  - a handle is bound to one device, owns a growable device workspace, and is not re-entrant;
+ *    distinct handles are independent.
+ *  - packed text: `text` = all dialogues' UTF-8 bytes back to back, `offs` = int64[n_rows+1] byte
+ *    offsets (offs[0] may be > 0).  `text` must be 16-byte aligned and readable up to the next
+ *    multiple of 16 past offs[n_rows] (the kernels stage 16-byte-aligned windows with TMA bulk
+ *    copies).
+ */
+#ifndef FDB200_H
+#define FDB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FD_OK 0
+#define FD_ERR_INVALID (-1)  /* bad argument */
+#define FD_ERR_CAPACITY (-2) /* caller buffer too small; required size reported */
+#define FD_ERR_CUDA (-3)     /* CUDA runtime error, text in fd_last_error */
+#define FD_ERR_STATE (-4)    /* a model piece needed by the call has not been set */
+#define FD_ERR_LIMIT (-5)    /* a dialogue exceeds a documented size limit */
+
+/* flags for fd_featurize / fd_transform */
+#define FD_FLAG_CLEAN 1u /* apply the caller-side cleaning lower + regexp_replace("[^a-zA-Z ]","")
+                            (utils/agent_api.py:143-144) inside the kernel; without it the input is
+                            the `clean_text` column and only the Tokenizer's ASCII lower-casing and
+                            Java "\\s" split are applied */
+
+/* classifier kinds for fd_set_forest */
+#define FD_KIND_DT 1  /* DecisionTreeClassificationModel  (fraud_detection_spark.py:59-65) */
+#define FD_KIND_RF 2  /* RandomForestClassificationModel  (fraud_detection_spark.py:67-74) */
+#define FD_KIND_GBT 3 /* GBTClassificationModel           (BASELINE.json config 4) */
+
+typedef struct fd_handle fd_handle;
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+/* Replaces SparkSession.builder...getOrCreate() + PipelineModel.load's JVM-side object
+ * (utils/agent_api.py:126-129): creates the per-device context that holds the uploaded model. */
+int fd_create(int device, fd_handle** out);
+int fd_destroy(fd_handle* h);
+const char* fd_last_error(fd_handle* h);
+int fd_version(void);
+
+/* ---- model upload (host pointers, synchronous) ---------------------------------------------- */
+/* StopWordsRemover params (stages/1_StopWordsRemover_8c0b00b256b3/metadata/part-00000:1).
+ * words = UTF-8 bytes back to back, offs = int32[n_words+1].  With case_sensitive == 0 ASCII
+ * letters of the list are folded to lower case (the host folds non-ASCII ones before the call). */
+int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, int32_t n_words,
+                     int32_t case_sensitive);
+/* HashingTF params (stages/2_HashingTF_e7eba1072633/metadata/part-00000:1): numFeatures, binary. */
+int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary);
+/* HashingTF.indexOf(term) for n terms on the HOST (no device work): out[i] = nonNegativeMod(
+ * murmur3_x86_32(term_i bytes, seed 42), num_features).  terms = bytes back to back, offs int32[n+1]. */
+int fd_hash_terms(const uint8_t* terms, const int32_t* offs, int32_t n, int32_t num_features, int32_t* out);
+/* IDFModel.idf (stages/3_IDF_58bd96296a82/data): dense f64[num_features]; NULL removes the stage. */
+int fd_set_idf(fd_handle* h, const double* idf, int32_t num_features);
+/* Binomial LogisticRegressionModel (stages/4_LogisticRegression_65ef69d6dfd9): dense coefficient
+ * row f64[num_features] (zeros where the saved sparse matrix has none), intercept, threshold. */
+int fd_set_linear(fd_handle* h, const double* coef_dense, int32_t num_features, double intercept,
+                  double threshold);
+/* Tree ensemble as SoA node arrays (Spark NodeData order: per tree pre-order ids, root first).
+ * tree_offsets int32[n_trees+1] indexes the concatenated node arrays; feature[n] < 0 marks a leaf;
+ * left/right are node ids LOCAL to the tree.  leaf_value: f64[n_nodes, n_classes] class-weight stats
+ * for FD_KIND_DT / FD_KIND_RF, f64[n_nodes] predictions for FD_KIND_GBT.  tree_weights f64[n_trees]
+ * (used by GBT only).  Replaces {DecisionTree,RandomForest,GBT}ClassificationModel.transform
+ * (fraud_detection_spark.py:98 on the models built at :59-74). */
+int fd_set_forest(fd_handle* h, int32_t kind, int32_t n_trees, const int32_t* tree_offsets,
+                  const int32_t* feature, const double* threshold, const int32_t* left,
+                  const int32_t* right, const double* leaf_value, const double* tree_weights,
+                  int32_t n_classes);
+
+/* ---- featurise: Tokenizer -> StopWordsRemover -> HashingTF -> IDF  (fraud_detection_spark.py:50-53;
+ *      saved stages 0..3) -------------------------------------------------------------------- */
+/* Pass 1: tokenise/hash/count every dialogue into the handle's workspace and report the total number
+ * of non-zeros through *nnz_host (this call synchronises `stream` to read it back). */
+int fd_featurize_begin(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev, int64_t n_rows,
+                       uint32_t flags, int64_t* nnz_host, void* stream);
+/* Pass 2: emit CSR for the rows of the last fd_featurize_begin: rowptr int64[n_rows+1],
+ * idx int32[nnz] ascending per row, val f64[nnz] (term count x idf).  capacity = elements available in
+ * out_idx/out_val; FD_ERR_CAPACITY if smaller than nnz. */
+int fd_featurize_finish(fd_handle* h, int64_t* out_rowptr_dev, int32_t* out_idx_dev, double* out_val_dev,
+                        int64_t capacity, void* stream);
+/* Both passes in one call; *nnz_host receives the total (also on FD_ERR_CAPACITY). */
+int fd_featurize(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev, int64_t n_rows,
+                 uint32_t flags, int64_t* out_rowptr_dev, int32_t* out_idx_dev, double* out_val_dev,
+                 int64_t capacity, int64_t* nnz_host, void* stream);
+
+/* ---- score: classifier stage on CSR features  (ProbabilisticClassificationModel.transform;
+ *      result columns read at utils/agent_api.py:161-167, fraud_detection_spark.py:101-118) ---- */
+/* out_pred f64[n_rows], out_prob f64[n_rows, n_classes], out_raw f64[n_rows, n_classes]. */
+int fd_score(fd_handle* h, const int64_t* rowptr_dev, const int32_t* idx_dev, const double* val_dev,
+             int64_t n_rows, double* out_pred_dev, double* out_prob_dev, double* out_raw_dev, void* stream);
+
+/* ---- transform: the whole PipelineModel.transform, fused (utils/agent_api.py:158) ----------- */
+/* text -> prediction / probability / rawPrediction without materialising the sparse vectors. */
+int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev, int64_t n_rows,
+                 uint32_t flags, double* out_pred_dev, double* out_prob_dev, double* out_raw_dev,
+                 void* stream);
+/* fd_transform / fd_featurize_* are asynchronous; a dialogue over the size limit (more than ~196k
+ * distinct hashed terms) is only detected on the device.  fd_status synchronises `stream` and returns
+ * (and clears) that sticky status: FD_OK or FD_ERR_LIMIT. */
+int fd_status(fd_handle* h, void* stream);
+/* Same with HOST buffers (pinned memory recommended): the call chunks the batch, overlaps the
+ * host->device copies, the kernels and the device->host copies on internal streams, and returns when
+ * the three result columns are complete in host memory.  text_host needs no padding or alignment. */
+int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* offs_host, int64_t n_rows,
+                      uint32_t flags, double* out_pred_host, double* out_prob_host, double* out_raw_host);
+/* Number of kernel launches the handle has issued since creation (bench.py's gpu_launches). */
+int64_t fd_launch_count(fd_handle* h);
+
+/* ---- RandomForest training: ml.tree.impl.RandomForest.run reached via Pipeline.fit
+ *      (fraud_detection_spark.py:85-91) ----------------------------------------------------- */
+/* TreePoint binning: bin[k] = lower_bound(thresholds of feature idx[k], val[k]) as u8.
+ * thr_ptr int32[num_features+1] indexes thr f64[]. */
+int fd_bin_csr(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int64_t nnz,
+               const int32_t* thr_ptr_dev, const double* thr_dev, uint8_t* out_bin_dev, void* stream);
+/* binSeqOp over a node group: for every work item w = (tree, node, feature) accumulate
+ * hist[w, bin, class] += bag weight over the explicit entries of that feature's column whose row sits
+ * in that node.  Columns are CSC over this rank's row shard: colptr int64[num_features+1],
+ * rowidx int32[nnz], bin u8[nnz].  label u8[n_rows], bagw u8[n_trees, n_rows],
+ * node_id int32[n_trees, n_rows] (current node of each row in each tree, heap numbering, root 1).
+ * item_tree/item_node/item_feat int32[n_items]; out_hist u32[n_items, 32, 2] is zeroed by the call.
+ * The implied zero-valued entries are NOT added here (fd_rf_best_split adds them after the
+ * cross-rank sum, from the node totals). */
+int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowidx_dev,
+                    const uint8_t* bin_dev, const uint8_t* label_dev, const uint8_t* bagw_dev,
+                    const int32_t* node_id_dev, int64_t n_rows, int32_t n_items,
+                    const int32_t* item_tree_dev, const int32_t* item_node_dev,
+                    const int32_t* item_feat_dev, uint32_t* out_hist_dev, void* stream);
+/* binsToBestSplit for a node group.  Items of one node are contiguous: node_item_ptr int32[n_nodes+1].
+ * node_total f64[n_nodes, 2] = class totals of each node (already summed over ranks);
+ * n_splits int32[num_features], bin_of_zero u8[num_features].
+ * Outputs per node: best_item int32 (-1: no valid split), best_split int32, best_gain f64,
+ * left/right class counts f64[n_nodes, 2]. */
+int fd_rf_best_split(fd_handle* h, const uint32_t* hist_dev, int32_t n_nodes, const int32_t* node_item_ptr_dev,
+                     const int32_t* item_feat_dev, const double* node_total_dev, const int32_t* n_splits_dev,
+                     const uint8_t* bin_of_zero_dev, int32_t min_instances, double min_info_gain,
+                     int32_t* out_best_item_dev, int32_t* out_best_split_dev, double* out_best_gain_dev,
+                     double* out_left_dev, double* out_right_dev, void* stream);
+/* Move rows to their children after a level: for each split node s (tree, node, feature, split bin):
+ * rows of that node go to 2*node if bin(feature) <= split bin else 2*node+1 (absent feature ->
+ * bin_of_zero).  Also accumulates the children's class totals (bag-weighted) into
+ * out_child_total f64[n_split_nodes, 2(left/right), 2(class)] (zeroed by the call). */
+int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowidx_dev, const uint8_t* bin_dev,
+                  const uint8_t* label_dev, const uint8_t* bagw_dev, int32_t* node_id_dev, int64_t n_rows,
+                  int32_t n_trees, int32_t n_split_nodes, const int32_t* split_tree_dev,
+                  const int32_t* split_node_dev, const int32_t* split_feat_dev, const int32_t* split_bin_dev,
+                  const uint8_t* bin_of_zero_dev, double* out_child_total_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FDB200_H */
