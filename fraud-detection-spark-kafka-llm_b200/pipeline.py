@@ -270,6 +270,10 @@ class PipelineModel:
                     batch = [batch]
                 texts = batch.tolist() if hasattr(batch, "tolist") else list(batch)
                 cleaned = False if cleaned is None else cleaned
+            if cleaned:
+                # Tokenizer applies String.toLowerCase to the whole string: the kernel folds ASCII, non-ASCII
+                # letters (rare after the reference's cleaning, which leaves only [a-z ]) are folded here
+                texts = [t.lower() if isinstance(t, str) and not t.isascii() else t for t in texts]
             pk = PackedText.from_strings(texts)
         return pk, (0 if cleaned else _lib.FD_FLAG_CLEAN)
 

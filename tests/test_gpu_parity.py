@@ -1,0 +1,160 @@
+"""GPU parity: the CUDA path, called through the C-ABI, against the CPU oracle on the same inputs.
+
+Bar (BASELINE.json north_star): hashed feature indices, term counts and predicted labels bit-exact;
+TF-IDF values bit-exact (one fp64 multiply); margins / votes bit-exact (same fp64 operation order);
+class probabilities within 1e-9 relative (they pass through exp(), whose last bit may differ between
+libm and CUDA)."""
+import importlib
+
+import numpy as np
+import pytest
+
+from helpers import csr_rows, messy_texts, oracle_for
+
+pytestmark = pytest.mark.gpu
+PROB_RTOL = 1e-9
+
+
+def _check_scores(res, exp, exact_raw=True):
+    pred, prob, raw = (res[k].cpu().numpy() if hasattr(res[k], "cpu") else res[k] for k in ("prediction", "probability", "rawPrediction"))
+    epred, eprob, eraw = exp
+    assert np.array_equal(pred, epred)
+    if exact_raw:
+        assert np.array_equal(raw, eraw)
+    else:
+        np.testing.assert_allclose(raw, eraw, rtol=PROB_RTOL, atol=0)
+    np.testing.assert_allclose(prob, eprob, rtol=PROB_RTOL, atol=1e-300)
+
+
+def test_shipped_lr_model_golden_texts(fd, shipped_model_dir, golden):
+    model = fd.PipelineModel.load(shipped_model_dir)
+    recs = golden["provisional_oracle_outputs"]
+    texts = [r["text"] for r in recs]
+    res = model.transform(texts)
+    raw = res["rawPrediction"].cpu().numpy()
+    for i, r in enumerate(recs):
+        assert raw[i, 1] == r["margin"], r["text"][:40]
+        assert res["prediction"][i].item() == r["prediction"]
+    _check_scores(res, oracle_for(model).transform([t.encode() for t in texts]))
+    # the agent-shaped call of utils/agent_api.py:155-175
+    long = [r for r in recs if r["n_tokens"] == 375][0]
+    out = fd.predict_and_get_label(model, long["text"])
+    assert out["prediction"] == 1.0 and abs(out["confidence"] - long["probability"][1]) <= 1e-9 * long["probability"][1]
+    rowptr, idx, val = model.featurize(texts)
+    for (ix, vl), r in zip(csr_rows(rowptr, idx, val), recs):
+        assert ix == r["idx"] and vl == r["val"]
+
+
+@pytest.mark.parametrize("num_features,binary", [(10000, False), (262144, False), (1000003, True), (1, False)])
+def test_featurize_messy_text_bit_exact(fd, num_features, binary):
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"), fd.StopWordsRemover(inputCol="words", outputCol="filtered"),
+              fd.HashingTF(inputCol="filtered", outputCol="raw_features", numFeatures=num_features, binary=binary)]
+    rng = np.random.default_rng(5)
+    idf = rng.random(num_features) * 3.0
+    idf[rng.integers(0, num_features, size=max(1, num_features // 10))] = 0.0
+    stages.append(fd.IDFModel(idf, inputCol="raw_features", outputCol="features"))
+    model = fd.PipelineModel(stages)
+    texts = messy_texts(700, seed=num_features % 97)
+    ora = oracle_for(model)
+    for cleaned in (False, True):
+        rowptr, idx, val = model.featurize(texts, cleaned=cleaned)
+        rows = csr_rows(rowptr, idx, val)
+        assert len(rows) == len(texts)
+        for t, (ix, vl) in zip(texts, rows):
+            src = t.lower().encode() if cleaned else t.encode()  # Tokenizer-only mode: non-ASCII case folding is the host's job
+            eix, evl, _, _ = ora.featurize(src, do_clean=not cleaned)
+            assert ix == eix, repr(t)
+            assert vl == evl, repr(t)
+
+
+def _long_rows():
+    rng = np.random.default_rng(11)
+    words = [bytes(rng.integers(97, 123, size=int(rng.integers(1, 9)), dtype=np.uint8)).decode() for _ in range(5000)]
+    rows = []
+    rows.append(" ".join(words[:3000]))                        # > 384 distinct buckets: wide-table kernel
+    rows.append(" ".join(words[i % 40] for i in range(4000)))  # many windows, few buckets
+    rows.append("x" * 5000 + " tail the end")                  # one token spanning several windows
+    rows.append("1" * 3000 + "ab" + "2" * 2000 + " cd")        # multi-window token that cleans down to "ab"
+    rows.append("7" * 2500 + " a b")                           # multi-window EMPTY token followed by letters
+    rows.append("a " + "9" * 2500)                             # trailing multi-window empty token (dropped)
+    rows.append(" " * 3000)                                    # separators only -> no tokens
+    rows.append(" " * 1500 + "z" + " " * 1500)                 # interior empties kept, trailing dropped
+    rows.append("the " * 1200)                                 # stop words only
+    rows.append("ok")
+    rows.append("word " * 205)                                 # token exactly at a window edge region
+    for k in (1008, 1009, 1023, 1024, 1025, 1040, 2047, 2048, 2049):
+        rows.append(("ab " * 400)[:k])
+        rows.append("q" * k)
+        rows.append("q" * (k - 1) + " r")
+    return rows
+
+
+def test_long_rows_windows_wide_table_and_giant_tokens(fd, shipped_model_dir):
+    model = fd.PipelineModel.load(shipped_model_dir)
+    rows = _long_rows()
+    ora = oracle_for(model)
+    rowptr, idx, val = model.featurize(rows)
+    for t, (ix, vl) in zip(rows, csr_rows(rowptr, idx, val)):
+        eix, evl, _, _ = ora.featurize(t.encode())
+        assert ix == eix and vl == evl, repr(t[:30]) + f" len={len(t)}"
+    _check_scores(model.transform(rows), ora.transform([t.encode() for t in rows]))
+
+
+def _tree_model(fd, kind, n_trees, depth, num_features=262144, seed=5):
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    rng = np.random.default_rng(seed)
+    corpus = synth.SynthCorpus(n_words=3000, seed=77)
+    feats = synth.hash_terms(corpus.words[corpus.n_stop:corpus.n_stop + 400] + [b""], num_features)
+    idf = np.log(1001.0 / (rng.integers(0, 1000, size=num_features) + 1.0))
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"), fd.StopWordsRemover(inputCol="words", outputCol="filtered_words"),
+              fd.HashingTF(inputCol="filtered_words", outputCol="raw_features", numFeatures=num_features),
+              fd.IDFModel(idf, inputCol="raw_features", outputCol="features")]
+    if kind == "dt":
+        cl = fd.DecisionTreeClassificationModel(synth.random_tree(rng, depth, feats, idf), num_features)
+    elif kind == "rf":
+        cl = fd.RandomForestClassificationModel([synth.random_tree(rng, depth, feats, idf, full=False) for _ in range(n_trees)], num_features)
+    else:
+        trees = [synth.random_tree(rng, depth, feats, idf, regression=True, full=False) for _ in range(n_trees)]
+        cl = fd.GBTClassificationModel(trees, [1.0] + [0.1] * (n_trees - 1), num_features)
+    return fd.PipelineModel(stages + [cl]), corpus
+
+
+@pytest.mark.parametrize("kind,n_trees,depth", [("dt", 1, 5), ("rf", 100, 10), ("rf", 33, 4), ("gbt", 200, 6), ("gbt", 7, 3)])
+def test_tree_models_fused_and_csr_paths(fd, kind, n_trees, depth, tmp_path):
+    model, corpus = _tree_model(fd, kind, n_trees, depth)
+    pk, _ = corpus.sample(300, tokens=120, device="cpu", seed=9)
+    data, offs = pk.data.numpy(), pk.offs.numpy()
+    rows = [bytes(data[offs[i]:offs[i + 1]]) for i in range(300)] + [t.encode() for t in messy_texts(100, seed=4)]
+    exp = oracle_for(model).transform(rows)
+    _check_scores(model.transform(rows), exp)
+    rowptr, idx, val = model.featurize(rows)
+    _check_scores(model.score(rowptr, idx, val), exp)
+    # Spark-format round trip of the tree stage (writer + loader) leaves the scores unchanged
+    model.save(str(tmp_path / "m"))
+    again = fd.PipelineModel.load(str(tmp_path / "m"))
+    _check_scores(again.transform(rows), exp)
+    assert len(np.unique(exp[2][:, 1])) > 3, "degenerate test: every row reached the same leaves"
+    if (kind, n_trees) in (("dt", 1), ("rf", 100), ("gbt", 200)):
+        assert not np.all(exp[0] == exp[0][0]), "degenerate test: all rows got one label"
+
+
+def test_host_buffer_transform_matches_device(fd):
+    model, corpus = _tree_model(fd, "dt", 1, 5)
+    pk, _ = corpus.sample(20000, tokens=50, device="cpu", seed=21)
+    dev = model.transform(pk, cleaned=False)
+    host = model.transform(pk, cleaned=False, output="host")
+    for k in ("prediction", "probability", "rawPrediction"):
+        assert np.array_equal(dev[k].cpu().numpy(), host[k])
+    assert model.handle().launch_count() > 0
+
+
+def test_empty_batch_and_errors(fd, shipped_model_dir):
+    model = fd.PipelineModel.load(shipped_model_dir)
+    assert model.transform([]).count() == 0
+    rowptr, idx, val = model.featurize([])
+    assert rowptr.tolist() == [0] and idx.numel() == 0
+    res = model.transform([""]).first()
+    assert res[0] == 0.0
+    h = fd.Handle(0)
+    with pytest.raises(fd.FdError):
+        h.call("fd_transform", None, None, 1, 1, None, None, None, None)
