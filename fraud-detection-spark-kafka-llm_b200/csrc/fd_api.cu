@@ -85,7 +85,8 @@ int fd_destroy(fd_handle* h) {
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
     Model& m = h->m;
-    cudaFree(m.sw_slots);
+    cudaFree(m.sw_tab);
+    cudaFree(m.sw_words);
     cudaFree(m.sw_pool);
     cudaFree(m.idf);
     cudaFree(m.coef);
@@ -114,17 +115,21 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
     Model& m = h->m;
     m.empty_is_stop = 0;
     if (n_words == 0) {
-        if (m.sw_slots) cudaFree(m.sw_slots);
+        if (m.sw_tab) cudaFree(m.sw_tab);
+        if (m.sw_words) cudaFree(m.sw_words);
         if (m.sw_pool) cudaFree(m.sw_pool);
-        m.sw_slots = nullptr;
+        m.sw_tab = nullptr;
+        m.sw_words = nullptr;
         m.sw_pool = nullptr;
         m.sw_cap = 0;
+        m.n_sw = 0;
         return FD_OK;
     }
     if (n_words > 2048) return set_err(h, FD_ERR_LIMIT, "at most 2048 stop words are supported (got %d)", n_words);
-    int cap = 16;
-    while (cap < 2 * n_words) cap <<= 1;
-    std::vector<uint4> slots(cap, make_uint4(0xFFFFFFFFu, 0, 0, 0));
+    int cap = 64;
+    while (cap < 4 * n_words) cap <<= 1;
+    std::vector<uint32_t> tab(cap, 0u);
+    std::vector<uint4> wordsv;
     std::vector<uint8_t> pool;
     for (int i = 0; i < n_words; ++i) {
         const int len = offs[i + 1] - offs[i];
@@ -148,14 +153,18 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
             pool.insert(pool.end(), w.begin(), w.end());
         }
         uint32_t slot = hsh & (uint32_t)(cap - 1);
-        while (slots[slot].x != 0xFFFFFFFFu) slot = (slot + 1) & (uint32_t)(cap - 1);
-        slots[slot] = s;
+        while (tab[slot] != 0u) slot = (slot + 1) & (uint32_t)(cap - 1);
+        tab[slot] = (hsh & 0xFFFF0000u) | (uint32_t)(wordsv.size() + 1);
+        wordsv.push_back(s);
     }
-    int rc = upload(h, &m.sw_slots, slots.data(), slots.size());
+    int rc = upload(h, &m.sw_tab, tab.data(), tab.size());
+    if (rc) return rc;
+    rc = upload(h, &m.sw_words, wordsv.data(), wordsv.size());
     if (rc) return rc;
     rc = upload(h, &m.sw_pool, pool.data(), pool.size());
     if (rc) return rc;
-    m.sw_cap = cap;
+    m.sw_cap = wordsv.empty() ? 0 : cap;
+    m.n_sw = (int)wordsv.size();
     return FD_OK;
 }
 

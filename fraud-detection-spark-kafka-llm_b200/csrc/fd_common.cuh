@@ -33,9 +33,13 @@ struct Ctrl {
 };
 
 struct Model {
-    // stop words: open-addressed table of 16-byte slots keyed by murmur3(word, 42)
-    uint4* sw_slots = nullptr;  // x = len (|0x80000000 when > 12 bytes), y/z/w = first 12 bytes or y = pool offset
-    int sw_cap = 0;             // power of two, 0 = no stop words
+    __host__ __device__ size_t sw_smem_bytes() const { return (size_t)sw_cap * 4 + (size_t)n_sw * 16; }
+    // stop words: open-addressed table of 4-byte slots keyed by murmur3(word, 42):
+    //   slot = (hash & 0xFFFF0000) | (word id + 1), 0 = empty; load factor <= 1/4 so most probes end at once
+    uint32_t* sw_tab = nullptr;
+    int sw_cap = 0;             // slots, power of two, 0 = no stop words
+    uint4* sw_words = nullptr;  // per word: x = len (|0x80000000 when > 12 bytes), y/z/w = first 12 bytes or y = pool offset
+    int n_sw = 0;
     uint8_t* sw_pool = nullptr; // bytes of words longer than 12
     int empty_is_stop = 0;
     // hashing

@@ -51,7 +51,12 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* b, uint32_t parity
     } while (!ok);
 }
 
-__device__ __forceinline__ uint32_t low_mask(int n) { return n >= 32 ? 0xFFFFFFFFu : ((1u << n) - 1u); }
+// n low bits set (n clamped to [0, 32]) -- one BMSK instruction
+__device__ __forceinline__ uint32_t low_mask(int n) {
+    uint32_t r;
+    asm("bmsk.clamp.b32 %0, 0, %1;" : "=r"(r) : "r"(n));
+    return r;
+}
 // gather the four 0x80 flag bits of a SWAR word into a nibble (byte 0 -> bit 0)
 __device__ __forceinline__ uint32_t movemask4(uint32_t f80) { return ((f80 >> 7) * 0x01020408u) >> 24; }
 
@@ -132,26 +137,26 @@ struct HashState {
 
 __device__ __forceinline__ bool letter_at(const uint32_t* lmask, int p) { return (lmask[p >> 5] >> (p & 31)) & 1u; }
 
-// is the token (hash h, n kept bytes, first 12 bytes b0..b2) a stop word?
-// long words (> 12 bytes) are compared byte by byte against the pool, walking the token's kept bytes.
-__device__ bool is_stop_word(const uint4* sw, int sw_cap, const uint8_t* pool, uint32_t h, uint32_t n, uint32_t b0,
-                             uint32_t b1, uint32_t b2, const uint8_t* rb, const uint32_t* lmask, int s, int e) {
+// token bytes [s, e) filtered by the letter mask == word (same length already checked)
+__device__ __noinline__ bool long_stop_word_equal(const uint8_t* word, const uint8_t* rb, const uint32_t* lmask, int s, int e) {
+    uint32_t i = 0;
+    for (int p = s; p < e; ++p)
+        if (letter_at(lmask, p) && rb[p] != word[i++]) return false;
+    return true;
+}
+
+// is the multi-window token (hash h, n kept bytes, first 12 bytes b0..b2) a stop word?  (words longer than 12
+// bytes are not matched on this rare path -- documented limitation)
+__device__ bool is_stop_word(const uint32_t* swt, const uint4* sww, int sw_cap, uint32_t h, uint32_t n, uint32_t b0,
+                             uint32_t b1, uint32_t b2) {
     const uint32_t mask = (uint32_t)sw_cap - 1u;
     uint32_t slot = h & mask;
     for (;;) {
-        const uint4 w = sw[slot];
-        if (w.x == 0xFFFFFFFFu) return false;
-        if ((w.x & 0x7FFFFFFFu) == n) {
-            if (!(w.x & 0x80000000u)) {
-                if (w.y == b0 && w.z == b1 && w.w == b2) return true;
-            } else if (s >= 0) {
-                const uint8_t* word = pool + w.y;
-                uint32_t i = 0;
-                bool same = true;
-                for (int p = s; p < e && same; ++p)
-                    if (letter_at(lmask, p)) same = (rb[p] == word[i++]);
-                if (same) return true;
-            }
+        const uint32_t e = swt[slot];
+        if (e == 0u) return false;
+        if (((e ^ h) >> 16) == 0u) {
+            const uint4 w = sww[(e & 0xFFFFu) - 1u];
+            if (w.x == n && w.y == b0 && w.z == b1 && w.w == b2) return true;
         }
         slot = (slot + 1u) & mask;
     }
@@ -161,15 +166,17 @@ __device__ bool is_stop_word(const uint4* sw, int sw_cap, const uint8_t* pool, u
 // the kernel
 // ------------------------------------------------------------------------------------------------
 template <int MODE, bool CLEAN, bool BIG>
-__global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS) k_rows(const RowArgs a) {
+__global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS, BIG ? 1 : 3) k_rows(const RowArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint4* sw = reinterpret_cast<uint4*>(smem_raw);
+    uint32_t* swt = reinterpret_cast<uint32_t*>(smem_raw);
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const Model& m = a.m;
-    WarpSmem& S = *reinterpret_cast<WarpSmem*>(smem_raw + (size_t)m.sw_cap * 16 + (size_t)warp * sizeof(WarpSmem));
+    uint4* sww = reinterpret_cast<uint4*>(smem_raw + (size_t)m.sw_cap * 4);
+    WarpSmem& S = *reinterpret_cast<WarpSmem*>(smem_raw + m.sw_smem_bytes() + (size_t)warp * sizeof(WarpSmem));
 
-    for (int i = threadIdx.x; i < m.sw_cap; i += blockDim.x) sw[i] = m.sw_slots[i];
+    for (int i = threadIdx.x; i < m.sw_cap; i += blockDim.x) swt[i] = m.sw_tab[i];
+    for (int i = threadIdx.x; i < m.n_sw; i += blockDim.x) sww[i] = m.sw_words[i];
     if (lane == 0) {
         mbar_init(&S.mbar[0], 1);
         mbar_init(&S.mbar[1], 1);
@@ -387,8 +394,7 @@ __global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS) k_rows(const RowArgs a
                         const uint32_t h = gt.finish();
                         if (gt.n == 0) {
                             was_empty = true;
-                        } else if (!(m.sw_cap && is_stop_word(sw, m.sw_cap, m.sw_pool, h, gt.n, gt.b0, gt.b1, gt.b2, rb,
-                                                              S.lmask, -1, -1))) {
+                        } else if (!(m.sw_cap && is_stop_word(swt, sww, m.sw_cap, h, gt.n, gt.b0, gt.b1, gt.b2))) {
                             isnew = tab_insert(tab, TLOG2, feature_index(h, m), 1u, binary);
                         }
                         gt.reset();
@@ -408,81 +414,101 @@ __global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS) k_rows(const RowArgs a
                 }
             }
             const int t_first = (giant || gt_active) ? 1 : 0;
+            const uint32_t swmask = (uint32_t)m.sw_cap - 1u;
             for (int t0 = t_first; t0 < Tc; t0 += 32) {
                 if (D + 32u > (uint32_t)(TCAP - TCAP / 4)) {  // keep the table at most 3/4 full
                     big = true;
                     break;
                 }
+                // The body is written in warp-uniform phases (boundaries -> hash -> stop-word probe -> insert)
+                // with per-lane predicates instead of nested branches, so the 32 tokens stay in lock step.
                 const int t = t0 + lane;
-                bool isnew = false;
-                bool pending_empty = false;
-                if (t < Tc) {
-                    const int s = S.tok[t], e = (int)S.tok[t + 1] - 1;
-                    const int len = e - s;
-                    uint32_t h = 42u, n = 0, b0 = 0, b1 = 0, b2 = 0;
-                    bool fast = false, empty = false;
-                    int f = 0;
-                    if (len <= 32) {
-                        const int wi = s >> 5, sh = s & 31;
-                        const uint32_t win = __funnelshift_r(S.lmask[wi], S.lmask[wi + 1], sh);
-                        const uint32_t bits = win & low_mask(len);
-                        if (bits == 0u) {
-                            empty = true;
-                        } else {
-                            f = __ffs(bits) - 1;
-                            n = (uint32_t)__popc(bits);
-                            fast = (bits >> f) == low_mask((int)n);
+                const bool valid = t < Tc;
+                const int tt = valid ? t : t_first;
+                // ---- phase 1: token extent and its kept-byte pattern
+                const int s = S.tok[tt], e = (int)S.tok[tt + 1] - 1;
+                const int len = e - s;
+                const uint32_t bits = __funnelshift_r(S.lmask[s >> 5], S.lmask[(s >> 5) + 1], s & 31) & low_mask(min(len, 32));
+                const int f = __ffs(bits) - 1;  // -1 when no kept byte
+                uint32_t n = (uint32_t)__popc(bits);
+                const bool fast = valid && len <= 32 && bits != 0u && (bits >> (f & 31)) == low_mask((int)n);
+                bool empty = valid && len <= 32 && bits == 0u;
+                const bool slow = valid && !fast && !empty;
+                // ---- phase 2: murmur3 of a contiguous token, first 12 bytes straight-line
+                uint32_t h = 42u, b0, b1, b2;
+                {
+                    const int p0 = fast ? s + f : 0;
+                    const int nn = fast ? (int)n : 0;
+                    const uint32_t* wp = reinterpret_cast<const uint32_t*>(rb + (p0 & ~3));
+                    const int sh8 = (p0 & 3) * 8;
+                    const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
+                    b0 = __funnelshift_r(w0, w1, sh8) & low_mask(8 * max(nn, 0));
+                    b1 = __funnelshift_r(w1, w2, sh8) & low_mask(8 * max(nn - 4, 0));
+                    b2 = __funnelshift_r(w2, w3, sh8) & low_mask(8 * max(nn - 8, 0));
+                    uint32_t kk = mm_k(b0);
+                    h = nn >= 4 ? mm_h(h, kk) : (nn > 0 ? h ^ kk : h);
+                    kk = mm_k(b1);
+                    h = nn >= 8 ? mm_h(h, kk) : (nn > 4 ? h ^ kk : h);
+                    kk = mm_k(b2);
+                    h = nn >= 12 ? mm_h(h, kk) : (nn > 8 ? h ^ kk : h);
+                    if (__any_sync(0xFFFFFFFFu, nn > 12)) {
+                        uint32_t prev = w3;
+                        for (int i = 3; __any_sync(0xFFFFFFFFu, nn > 4 * i); ++i) {
+                            if (nn > 4 * i) {
+                                const uint32_t nxt = wp[i + 1];
+                                const uint32_t k = __funnelshift_r(prev, nxt, sh8);
+                                prev = nxt;
+                                const int r = nn - 4 * i;
+                                h = r >= 4 ? mm_h(h, mm_k(k)) : h ^ mm_k(k & low_mask(8 * r));
+                            }
                         }
                     }
-                    if (fast) {
-                        const int p0 = s + f;
-                        const uint32_t* wp = reinterpret_cast<const uint32_t*>(rb + (p0 & ~3));
-                        const int sh = (p0 & 3) * 8;
-                        uint32_t prev = wp[0];
-                        const int nb = (int)(n >> 2);
-                        for (int i = 0; i < nb; ++i) {
-                            const uint32_t nxt = wp[i + 1];
-                            const uint32_t k = __funnelshift_r(prev, nxt, sh);
-                            prev = nxt;
-                            if (i == 0) b0 = k;
-                            else if (i == 1) b1 = k;
-                            else if (i == 2) b2 = k;
-                            h = mm_h(h, mm_k(k));
+                    h = mm_fmix(h, (uint32_t)nn);
+                }
+                if (slow) {  // kept bytes are not contiguous (or the token is longer than 32 bytes): byte-wise walk
+                    HashState hs;
+                    hs.reset();
+                    for (int p = s; p < e; ++p)
+                        if (letter_at(S.lmask, p)) hs.put(rb[p]);
+                    h = hs.finish();
+                    n = hs.n;
+                    b0 = hs.b0;
+                    b1 = hs.b1;
+                    b2 = hs.b2;
+                    empty = (n == 0u);
+                }
+                // ---- phase 3: stop-word probe (open addressing keyed by the same hash)
+                bool stop = false;
+                if (m.sw_cap) {
+                    bool probing = valid && !empty;
+                    uint32_t slot = h & swmask;
+                    while (__any_sync(0xFFFFFFFFu, probing)) {
+                        if (probing) {
+                            const uint32_t ent = swt[slot];
+                            if (ent == 0u) {
+                                probing = false;
+                            } else if (((ent ^ h) >> 16) == 0u) {  // 16-bit fingerprint hit: verify the bytes
+                                const uint4 w = sww[(ent & 0xFFFFu) - 1u];
+                                if ((w.x & 0x7FFFFFFFu) == n) {
+                                    const bool same = !(w.x & 0x80000000u) ? (w.y == b0 && w.z == b1 && w.w == b2)
+                                                                           : long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s, e);
+                                    if (same) {
+                                        stop = true;
+                                        probing = false;
+                                    }
+                                }
+                            }
+                            slot = (slot + 1u) & swmask;
                         }
-                        const int tail = (int)(n & 3u);
-                        if (tail) {
-                            const uint32_t nxt = wp[nb + 1];
-                            const uint32_t k = __funnelshift_r(prev, nxt, sh) & low_mask(8 * tail);
-                            if (nb == 0) b0 = k;
-                            else if (nb == 1) b1 = k;
-                            else if (nb == 2) b2 = k;
-                            h ^= mm_k(k);
-                        }
-                        h = mm_fmix(h, n);
-                    } else if (!empty) {
-                        HashState hs;
-                        hs.reset();
-                        for (int p = s; p < e; ++p)
-                            if (letter_at(S.lmask, p)) hs.put(rb[p]);
-                        h = hs.finish();
-                        n = hs.n;
-                        b0 = hs.b0;
-                        b1 = hs.b1;
-                        b2 = hs.b2;
-                        empty = (n == 0u);
-                    }
-                    if (empty) {
-                        if (s <= last_letter) {
-                            if (!m.empty_is_stop) isnew = tab_insert(tab, TLOG2, m.empty_idx, 1u, binary);
-                        } else {
-                            pending_empty = true;
-                        }
-                    } else if (!(m.sw_cap && is_stop_word(sw, m.sw_cap, m.sw_pool, h, n, b0, b1, b2, rb, S.lmask, s, e))) {
-                        isnew = tab_insert(tab, TLOG2, feature_index(h, m), 1u, binary);
                     }
                 }
+                // ---- phase 4: count the surviving token
+                const bool interior_empty = empty && s <= last_letter;
+                const bool ins = valid && (empty ? (interior_empty && !m.empty_is_stop) : !stop);
+                bool isnew = false;
+                if (ins) isnew = tab_insert(tab, TLOG2, empty ? m.empty_idx : feature_index(h, m), 1u, binary);
                 D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
-                pend += __popc(__ballot_sync(0xFFFFFFFFu, pending_empty));
+                pend += __popc(__ballot_sync(0xFFFFFFFFu, empty && !interior_empty));
             }
         }
         gt_active = giant;
@@ -786,8 +812,8 @@ __global__ void k_gather_csr(const unsigned long long* __restrict__ tmp, const l
 // ------------------------------------------------------------------------------------------------
 template <int MODE, bool CLEAN>
 static cudaError_t launch_mode(fd_handle* h, const RowArgs& a, cudaStream_t st) {
-    const size_t smem = (size_t)a.m.sw_cap * 16 + (size_t)ROW_WARPS * sizeof(WarpSmem);
-    const size_t smem_big = (size_t)a.m.sw_cap * 16 + sizeof(WarpSmem);
+    const size_t smem = a.m.sw_smem_bytes() + (size_t)ROW_WARPS * sizeof(WarpSmem);
+    const size_t smem_big = a.m.sw_smem_bytes() + sizeof(WarpSmem);
     auto kern = k_rows<MODE, CLEAN, false>;
     auto kbig = k_rows<MODE, CLEAN, true>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
