@@ -6,8 +6,8 @@ module at the repository root."""
 from . import spark_format
 from ._lib import FdError, Handle, LIB_PATH, load_library
 from .packing import PackedText, pack_strings
-from .pipeline import PipelineModel, Row, TransformResult, predict_and_get_label
-from .stages import (DecisionTreeClassificationModel, GBTClassificationModel, HashingTF, IDF, IDFModel,
+from .pipeline import Pipeline, PipelineModel, Row, TransformResult, predict_and_get_label
+from .stages import (DecisionTreeClassificationModel, DecisionTreeClassifier, RandomForestClassifier, GBTClassificationModel, HashingTF, IDF, IDFModel,
                      LogisticRegressionModel, RandomForestClassificationModel, StopWordsRemover, Tokenizer,
                      load_default_stop_words, load_stage)
 

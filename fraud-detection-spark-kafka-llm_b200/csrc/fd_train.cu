@@ -1,0 +1,294 @@
+// fd_train.cu -- random-forest training kernels: TreePoint binning, per-node class-count histograms over
+// CSC columns (shared-memory atomics), Gini best-split selection, and the row -> child update.
+//
+// Restates ml.tree.impl.RandomForest (Spark 3.5.5) reached through Pipeline.fit at
+// fraud_detection_spark.py:85-91 with the classifiers built at :59-74.  Spark densifies every row to
+// numFeatures bins; here rows stay sparse: a histogram pass visits, for every (node, feature-in-subset)
+// item, only that feature's COLUMN (CSC over this rank's row shard) and keeps the entries whose row
+// currently sits in the node.  Rows without the feature are accounted for after the cross-rank sum:
+// hist[bin_of_zero] += node_total - sum(explicit), which is exact because all counts are integers.
+#include "fd_common.cuh"
+
+namespace fd {
+
+constexpr int HB = 32;  // bins per feature (maxBins)
+
+// ---- TreePoint.findBin: bin = lower_bound(thresholds of the feature, value) --------------------------
+__global__ void k_bin_csr(const int32_t* __restrict__ idx, const double* __restrict__ val, long long nnz,
+                          const int32_t* __restrict__ thr_ptr, const double* __restrict__ thr, uint8_t* __restrict__ out) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
+        const int f = idx[k];
+        const double v = val[k];
+        int lo = thr_ptr[f], hi = thr_ptr[f + 1];
+        const int base = lo;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (__ldg(thr + mid) < v) lo = mid + 1;
+            else hi = mid;
+        }
+        out[k] = (uint8_t)(lo - base);
+    }
+}
+
+// ---- binSeqOp: one warp per (item, column segment) ---------------------------------------------------
+// item = (tree, node, feature).  The warp walks its segment of the feature's column, keeps entries whose
+// row is in the node, and adds the row's bag weight to a warp-private shared-memory histogram
+// [32 bins][2 classes]; the non-zero cells are then added to the item's global histogram.
+__global__ void __launch_bounds__(256) k_rf_histogram(const int64_t* __restrict__ colptr, const int32_t* __restrict__ rowidx,
+                                                      const uint8_t* __restrict__ bin, const uint8_t* __restrict__ label,
+                                                      const uint8_t* __restrict__ bagw, const int32_t* __restrict__ node_id,
+                                                      long long n_rows, int n_units, const int32_t* __restrict__ unit_item,
+                                                      const int32_t* __restrict__ unit_seg, int seg_len,
+                                                      const int32_t* __restrict__ item_tree, const int32_t* __restrict__ item_node,
+                                                      const int32_t* __restrict__ item_feat, unsigned int* __restrict__ hist) {
+    __shared__ unsigned int sh[8][HB * 2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned int* h = sh[warp];
+    const int nwarps = gridDim.x * 8;
+    for (int u = blockIdx.x * 8 + warp; u < n_units; u += nwarps) {
+        h[lane] = 0u;
+        h[32 + lane] = 0u;
+        __syncwarp();
+        const int item = unit_item[u];
+        const int t = item_tree[item], node = item_node[item], f = item_feat[item];
+        const long long c0 = colptr[f] + (long long)unit_seg[u] * seg_len;
+        const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
+        const int32_t* nid = node_id + (long long)t * n_rows;
+        const uint8_t* bw = bagw + (long long)t * n_rows;
+        for (long long e = c0 + lane; e < c1; e += 32) {
+            const int r = rowidx[e];
+            if (nid[r] == node) {
+                const unsigned int w = bw[r];
+                if (w) atomicAdd(&h[(int)bin[e] * 2 + (int)label[r]], w);
+            }
+        }
+        __syncwarp();
+        unsigned int* g = hist + (size_t)item * (HB * 2);
+        const unsigned int a = h[lane], b = h[32 + lane];
+        if (a) atomicAdd(g + lane, a);
+        if (b) atomicAdd(g + 32 + lane, b);
+        __syncwarp();
+    }
+}
+
+// ---- binsToBestSplit: one warp per node --------------------------------------------------------------
+__device__ __forceinline__ double gini2(double c0, double c1, double total) {
+    if (total == 0.0) return 0.0;
+    double imp = 1.0;
+    const double f0 = c0 / total;
+    imp = __dsub_rn(imp, __dmul_rn(f0, f0));
+    const double f1 = c1 / total;
+    imp = __dsub_rn(imp, __dmul_rn(f1, f1));
+    return imp;
+}
+
+constexpr double MIN_GAIN = -1.7976931348623157e308;  // Double.MinValue marks an invalid split
+
+__global__ void __launch_bounds__(128) k_rf_best_split(const unsigned int* __restrict__ hist, int n_nodes,
+                                                       const int32_t* __restrict__ node_item_ptr, const int32_t* __restrict__ item_feat,
+                                                       const double* __restrict__ node_total, const int32_t* __restrict__ n_splits,
+                                                       const uint8_t* __restrict__ bin_of_zero, int min_instances, double min_info_gain,
+                                                       int32_t* __restrict__ best_item, int32_t* __restrict__ best_split,
+                                                       double* __restrict__ best_gain, double* __restrict__ out_left,
+                                                       double* __restrict__ out_right) {
+    const int lane = threadIdx.x & 31;
+    const int node = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (node >= n_nodes) return;
+    const double t0 = node_total[2 * node], t1 = node_total[2 * node + 1];
+    const double ptotal = __dadd_rn(t0, t1);
+    const double pimp = gini2(t0, t1, ptotal);
+    double bg = MIN_GAIN, bl0 = 0, bl1 = 0;
+    int bi = -1, bs = -1;
+    for (int it = node_item_ptr[node] + lane; it < node_item_ptr[node + 1]; it += 32) {
+        const int f = item_feat[it];
+        const int ns = n_splits[f];
+        if (ns == 0) continue;
+        const unsigned int* h = hist + (size_t)it * (HB * 2);
+        // explicit totals, then the implied zero-valued rows go to bin_of_zero
+        unsigned int e0 = 0, e1 = 0;
+        for (int b = 0; b <= ns; ++b) {
+            e0 += h[2 * b];
+            e1 += h[2 * b + 1];
+        }
+        const double z0 = t0 - (double)e0, z1 = t1 - (double)e1;
+        const int bz = bin_of_zero[f];
+        double l0 = 0.0, l1 = 0.0, fg = MIN_GAIN, fl0 = 0, fl1 = 0;
+        int fs = -1;
+        for (int s = 0; s < ns; ++s) {  // cumulative left stats = bins 0..s
+            l0 += (double)h[2 * s] + (s == bz ? z0 : 0.0);
+            l1 += (double)h[2 * s + 1] + (s == bz ? z1 : 0.0);
+            const double r0 = t0 - l0, r1 = t1 - l1;
+            const double lc = __dadd_rn(l0, l1), rc = __dadd_rn(r0, r1);
+            double g;
+            if (lc < (double)min_instances || rc < (double)min_instances) {
+                g = MIN_GAIN;
+            } else {
+                const double tc = __dadd_rn(lc, rc);
+                const double lw = lc / tc, rw = rc / tc;
+                g = __dsub_rn(__dsub_rn(pimp, __dmul_rn(lw, gini2(l0, l1, lc))), __dmul_rn(rw, gini2(r0, r1, rc)));
+                if (g < min_info_gain) g = MIN_GAIN;
+            }
+            if (g > fg) {  // first maximum over splits
+                fg = g;
+                fs = s;
+                fl0 = l0;
+                fl1 = l1;
+            }
+        }
+        if (fs >= 0 && fg > bg) {  // first maximum over this lane's items (ascending item order)
+            bg = fg;
+            bi = it;
+            bs = fs;
+            bl0 = fl0;
+            bl1 = fl1;
+        }
+    }
+    // warp arg-max: larger gain wins, ties go to the smaller item index (= first in subset order)
+    for (int d = 16; d > 0; d >>= 1) {
+        const double og = __shfl_down_sync(0xFFFFFFFFu, bg, d);
+        const int oi = __shfl_down_sync(0xFFFFFFFFu, bi, d), os = __shfl_down_sync(0xFFFFFFFFu, bs, d);
+        const double o0 = __shfl_down_sync(0xFFFFFFFFu, bl0, d), o1 = __shfl_down_sync(0xFFFFFFFFu, bl1, d);
+        const bool take = oi >= 0 && (bi < 0 || og > bg || (og == bg && oi < bi));
+        if (take) {
+            bg = og;
+            bi = oi;
+            bs = os;
+            bl0 = o0;
+            bl1 = o1;
+        }
+    }
+    if (lane == 0) {
+        best_item[node] = bi;
+        best_split[node] = bs;
+        best_gain[node] = bi >= 0 ? bg : MIN_GAIN;
+        out_left[2 * node] = bl0;
+        out_left[2 * node + 1] = bl1;
+        out_right[2 * node] = t0 - bl0;
+        out_right[2 * node + 1] = t1 - bl1;
+    }
+}
+
+// ---- move rows to their children ------------------------------------------------------------------------
+// explicit entries of the split feature: one warp per (split node, column segment)
+__global__ void __launch_bounds__(256) k_rf_advance_explicit(const int64_t* __restrict__ colptr, const int32_t* __restrict__ rowidx,
+                                                             const uint8_t* __restrict__ bin, int32_t* __restrict__ node_id,
+                                                             long long n_rows, int n_units, const int32_t* __restrict__ unit_item,
+                                                             const int32_t* __restrict__ unit_seg, int seg_len,
+                                                             const int32_t* __restrict__ split_tree, const int32_t* __restrict__ split_node,
+                                                             const int32_t* __restrict__ split_feat, const int32_t* __restrict__ split_bin) {
+    const int lane = threadIdx.x & 31;
+    const int nwarps = gridDim.x * 8;
+    for (int u = blockIdx.x * 8 + (threadIdx.x >> 5); u < n_units; u += nwarps) {
+        const int s = unit_item[u];
+        const int node = split_node[s], f = split_feat[s], sb = split_bin[s];
+        int32_t* nid = node_id + (long long)split_tree[s] * n_rows;
+        const long long c0 = colptr[f] + (long long)unit_seg[u] * seg_len;
+        const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
+        for (long long e = c0 + lane; e < c1; e += 32) {
+            const int r = rowidx[e];
+            if (nid[r] == node) nid[r] = ((int)bin[e] <= sb) ? 2 * node : 2 * node + 1;
+        }
+    }
+}
+
+// rows still sitting in a split node do not have the feature: they follow bin_of_zero (action = child id),
+// rows of nodes that became leaves keep their id (action < 0)
+__global__ void k_rf_advance_default(int32_t* __restrict__ node_id, long long n_rows, int n_trees, int level_base,
+                                     const int32_t* __restrict__ action) {
+    const long long total = n_rows * n_trees;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
+        const int n = node_id[k];
+        if (n >= level_base && n < 2 * level_base) {
+            const int a = action[(k / n_rows) * level_base + (n - level_base)];
+            if (a >= 0) node_id[k] = a;
+        }
+    }
+}
+
+}  // namespace fd
+
+using namespace fd;
+
+extern "C" {
+
+int fd_bin_csr(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int64_t nnz, const int32_t* thr_ptr_dev,
+               const double* thr_dev, uint8_t* out_bin_dev, void* stream) {
+    if (!h) return FD_ERR_INVALID;
+    if (nnz < 0 || (nnz > 0 && (!idx_dev || !val_dev || !thr_ptr_dev || !out_bin_dev))) return set_err(h, FD_ERR_INVALID, "bad fd_bin_csr arguments");
+    if (nnz == 0) return FD_OK;
+    FD_CUDA(h, cudaSetDevice(h->device));
+    long long g = (nnz + 255) / 256;
+    if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
+    k_bin_csr<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>(idx_dev, val_dev, nnz, thr_ptr_dev, thr_dev, out_bin_dev);
+    h->launches += 1;
+    FD_CUDA(h, cudaGetLastError());
+    return FD_OK;
+}
+
+int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowidx_dev, const uint8_t* bin_dev,
+                    const uint8_t* label_dev, const uint8_t* bagw_dev, const int32_t* node_id_dev, int64_t n_rows,
+                    int32_t n_items, const int32_t* item_tree_dev, const int32_t* item_node_dev, const int32_t* item_feat_dev,
+                    int32_t n_units, const int32_t* unit_item_dev, const int32_t* unit_seg_dev, int32_t seg_len,
+                    uint32_t* out_hist_dev, void* stream) {
+    if (!h) return FD_ERR_INVALID;
+    if (n_items < 0 || n_units < 0 || seg_len <= 0 || !out_hist_dev) return set_err(h, FD_ERR_INVALID, "bad fd_rf_histogram arguments");
+    FD_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    FD_CUDA(h, cudaMemsetAsync(out_hist_dev, 0, (size_t)n_items * HB * 2 * sizeof(uint32_t), st));
+    if (n_units == 0) return FD_OK;
+    int g = (n_units + 7) / 8;
+    if (g > h->sm_count * 8) g = h->sm_count * 8;
+    k_rf_histogram<<<g, 256, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, label_dev, bagw_dev, node_id_dev, n_rows, n_units, unit_item_dev,
+                                      unit_seg_dev, seg_len, item_tree_dev, item_node_dev, item_feat_dev, out_hist_dev);
+    h->launches += 1;
+    FD_CUDA(h, cudaGetLastError());
+    return FD_OK;
+}
+
+int fd_rf_best_split(fd_handle* h, const uint32_t* hist_dev, int32_t n_nodes, const int32_t* node_item_ptr_dev,
+                     const int32_t* item_feat_dev, const double* node_total_dev, const int32_t* n_splits_dev,
+                     const uint8_t* bin_of_zero_dev, int32_t min_instances, double min_info_gain, int32_t* out_best_item_dev,
+                     int32_t* out_best_split_dev, double* out_best_gain_dev, double* out_left_dev, double* out_right_dev,
+                     void* stream) {
+    if (!h) return FD_ERR_INVALID;
+    if (n_nodes < 0) return set_err(h, FD_ERR_INVALID, "n_nodes < 0");
+    if (n_nodes == 0) return FD_OK;
+    FD_CUDA(h, cudaSetDevice(h->device));
+    k_rf_best_split<<<(n_nodes + 3) / 4, 128, 0, (cudaStream_t)stream>>>(hist_dev, n_nodes, node_item_ptr_dev, item_feat_dev, node_total_dev,
+                                                                        n_splits_dev, bin_of_zero_dev, min_instances, min_info_gain,
+                                                                        out_best_item_dev, out_best_split_dev, out_best_gain_dev,
+                                                                        out_left_dev, out_right_dev);
+    h->launches += 1;
+    FD_CUDA(h, cudaGetLastError());
+    return FD_OK;
+}
+
+int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowidx_dev, const uint8_t* bin_dev,
+                  int32_t* node_id_dev, int64_t n_rows, int32_t n_trees, int32_t level_base, int32_t n_split_nodes,
+                  const int32_t* split_tree_dev, const int32_t* split_node_dev, const int32_t* split_feat_dev,
+                  const int32_t* split_bin_dev, int32_t n_units, const int32_t* unit_item_dev, const int32_t* unit_seg_dev,
+                  int32_t seg_len, const int32_t* action_dev, void* stream) {
+    if (!h) return FD_ERR_INVALID;
+    if (n_split_nodes < 0 || n_units < 0 || seg_len <= 0 || level_base <= 0) return set_err(h, FD_ERR_INVALID, "bad fd_rf_advance arguments");
+    if (n_split_nodes == 0) return FD_OK;
+    FD_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_units > 0) {
+        int g = (n_units + 7) / 8;
+        if (g > h->sm_count * 8) g = h->sm_count * 8;
+        k_rf_advance_explicit<<<g, 256, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, node_id_dev, n_rows, n_units, unit_item_dev, unit_seg_dev,
+                                                 seg_len, split_tree_dev, split_node_dev, split_feat_dev, split_bin_dev);
+        h->launches += 1;
+    }
+    long long total = n_rows * n_trees;
+    long long g2 = (total + 255) / 256;
+    if (g2 > (long long)h->sm_count * 16) g2 = (long long)h->sm_count * 16;
+    k_rf_advance_default<<<(unsigned)g2, 256, 0, st>>>(node_id_dev, n_rows, n_trees, level_base, action_dev);
+    h->launches += 1;
+    FD_CUDA(h, cudaGetLastError());
+    return FD_OK;
+}
+
+}  // extern "C"

@@ -342,6 +342,55 @@ class PipelineModel:
         return TransformResult(dict(zip(names, (pred, prob, raw))), n)
 
 
+class Pipeline:
+    """``pyspark.ml.Pipeline``: ``Pipeline(stages=[...]).fit(batch)`` (reference fraud_detection_spark.py:85-91).
+
+    Supported shape: Tokenizer -> [StopWordsRemover] -> HashingTF -> [IDF | IDFModel] -> tree estimator / model.
+    Feature stages run through ``fd_featurize``; ``IDF.fit`` counts document frequencies on the device (summed
+    over ranks); the tree estimator trains with the fd_rf_* kernels.  Each rank passes ITS shard of rows."""
+
+    def __init__(self, stages: Sequence[S.Stage]):
+        self.stages = list(stages)
+
+    def getStages(self):
+        return self.stages
+
+    def fit(self, batch, labels=None, cleaned: Optional[bool] = None, device: Optional[int] = None, **explicit) -> PipelineModel:
+        torch = _torch()
+        import torch.distributed as dist
+        feats = [s for s in self.stages if isinstance(s, (S.Tokenizer, S.StopWordsRemover, S.HashingTF))]
+        idf = [s for s in self.stages if isinstance(s, (S.IDF, S.IDFModel))]
+        est = [s for s in self.stages if isinstance(s, (S._TreeEstimator, S.ClassificationModel))]
+        if len(idf) > 1 or len(est) > 1 or len(feats) + len(idf) + len(est) != len(self.stages):
+            raise ValueError("unsupported pipeline shape for the B200 path")
+        if isinstance(batch, dict) and labels is None and est:
+            labels = batch[est[0].getOrDefault("labelCol")]
+        tf_model = PipelineModel(feats)
+        rowptr, idx, val = tf_model.featurize(batch, cleaned=cleaned, device=device)
+        dev = rowptr.device
+        nf = int(tf_model._plan.hashing.getOrDefault("numFeatures"))
+        fitted: List[S.Stage] = list(feats)
+        if idf:
+            st = idf[0]
+            if isinstance(st, S.IDF):
+                df = torch.bincount(idx[val > 0].long(), minlength=nf)
+                nd = torch.tensor([rowptr.numel() - 1], dtype=torch.int64, device=dev)
+                if dist.is_available() and dist.is_initialized():
+                    dist.all_reduce(df)
+                    dist.all_reduce(nd)
+                st = st.fit_from_doc_freq(df.cpu().numpy(), int(nd.item()))
+            fitted.append(st)
+            val = val * torch.from_numpy(st.idf).to(dev)[idx.long()]  # IDFModel.transform: one exact fp64 multiply
+        if est:
+            c = est[0]
+            if isinstance(c, S._TreeEstimator):
+                lab = torch.as_tensor(np.asarray(labels), device=dev).to(torch.uint8)
+                c = c.fit_csr(tf_model.handle(device), rowptr, idx, val, lab, nf, **explicit)
+                c.paramMap.setdefault("featuresCol", fitted[-1].getOrDefault("outputCol"))
+            fitted.append(c)
+        return PipelineModel(fitted)
+
+
 def predict_and_get_label(model: PipelineModel, text: str) -> Dict[str, Any]:
     """The reference's ``DeepSeekClassificationAgent.predict_and_get_label`` (utils/agent_api.py:155-175) on
     this pipeline: raw dialogue in, ``{"prediction", "confidence"}`` out (confidence = probability[1])."""

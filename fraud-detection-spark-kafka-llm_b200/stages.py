@@ -366,6 +366,60 @@ class GBTClassificationModel(_EnsembleIO):
         self.numFeatures, self.numClasses = int(numFeatures), 2
 
 
+# ------------------------------------------------------------------------------------ estimators
+class _TreeEstimator(Stage):
+    """Shared ``fit_csr``: trains on this rank's CSR feature rows with the CUDA backend (all-reducing the
+    per-node histograms over the default process group when one is initialised)."""
+    n_trees_param = None
+
+    def _trainer(self, handle, n_features):
+        from .training import CudaTreeBackend, ForestTrainer
+        g = self.getOrDefault
+        n_trees = int(g("numTrees")) if self.n_trees_param else 1
+        return ForestTrainer(CudaTreeBackend(handle), n_features, n_trees=n_trees, max_depth=int(g("maxDepth")),
+                             max_bins=int(g("maxBins")), min_instances_per_node=int(g("minInstancesPerNode")),
+                             min_info_gain=float(g("minInfoGain")),
+                             feature_subset_strategy=str(g("featureSubsetStrategy")) if self.n_trees_param else "all",
+                             subsampling_rate=float(g("subsamplingRate")) if self.n_trees_param else 1.0, seed=int(g("seed")))
+
+    def fit_csr(self, handle, rowptr, idx, val, labels, n_features, **explicit):
+        if str(self.getOrDefault("impurity")).lower() != "gini":
+            raise ValueError("only impurity='gini' is implemented on this path")
+        trainer = self._trainer(handle, n_features)
+        trees = trainer.fit(rowptr, idx, val, labels, **explicit)
+        model = self._make_model(trees, n_features)
+        model.paramMap = {k: v for k, v in self.paramMap.items()}
+        model.trainer_stats = trainer.stats
+        return model
+
+
+class DecisionTreeClassifier(_TreeEstimator):
+    """``org.apache.spark.ml.classification.DecisionTreeClassifier`` (reference fraud_detection_spark.py:59-65)."""
+    spark_class = "org.apache.spark.ml.classification.DecisionTreeClassifier"
+    uid_prefix = "DecisionTreeClassifier"
+    defaults = dict(DecisionTreeClassificationModel.defaults)
+
+    def __init__(self, uid=None, **params):
+        super().__init__(uid, **params)
+
+    def _make_model(self, trees, n_features):
+        return DecisionTreeClassificationModel(trees[0], n_features, 2, uid=self.uid)
+
+
+class RandomForestClassifier(_TreeEstimator):
+    """``org.apache.spark.ml.classification.RandomForestClassifier`` (reference fraud_detection_spark.py:67-74)."""
+    spark_class = "org.apache.spark.ml.classification.RandomForestClassifier"
+    uid_prefix = "RandomForestClassifier"
+    n_trees_param = "numTrees"
+    defaults = dict(RandomForestClassificationModel.defaults)
+
+    def __init__(self, uid=None, **params):
+        super().__init__(uid, **params)
+
+    def _make_model(self, trees, n_features):
+        return RandomForestClassificationModel(trees, n_features, 2, uid=self.uid)
+
+
 STAGE_CLASSES = {c.spark_class: c for c in (Tokenizer, StopWordsRemover, HashingTF, IDF, IDFModel, LogisticRegressionModel,
                                              DecisionTreeClassificationModel, RandomForestClassificationModel,
                                              GBTClassificationModel)}

@@ -1,0 +1,120 @@
+"""Host-side training logic on CPU: findSplits against the oracle, and the multi-rank orchestration under gloo
+(world size 2) with the numpy stand-in backend -- both ranks must grow the oracle's trees."""
+import importlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import spark_oracle as so
+
+training = importlib.import_module("fraud-detection-spark-kafka-llm_b200.training")
+
+
+def _toy(n=240, f=40, seed=0):
+    """Small sparse rows with integer-ish tf-idf values and labels tied to a few features."""
+    rng = np.random.default_rng(seed)
+    idf = np.round(rng.random(f) * 3 + 0.1, 3)
+    rows_idx, rows_val, labels = [], [], []
+    for i in range(n):
+        k = int(rng.integers(0, 9))
+        ix = np.sort(rng.choice(f, size=k, replace=False))
+        cnt = rng.integers(1, 4, size=k)
+        y = int((3 in ix and cnt[list(ix).index(3)] > 1) or (7 in ix) or rng.random() < 0.1)
+        rows_idx.append(ix.tolist())
+        rows_val.append((cnt * idf[ix]).tolist())
+        labels.append(y)
+    return rows_idx, rows_val, np.asarray(labels, dtype=np.uint8), f
+
+
+def _csr(rows_idx, rows_val):
+    rowptr = np.zeros(len(rows_idx) + 1, dtype=np.int64)
+    np.cumsum([len(r) for r in rows_idx], out=rowptr[1:])
+    idx = np.asarray([x for r in rows_idx for x in r], dtype=np.int32)
+    val = np.asarray([x for r in rows_val for x in r], dtype=np.float64)
+    return torch.from_numpy(rowptr), torch.from_numpy(idx), torch.from_numpy(val)
+
+
+def _oracle_forest(rows_idx, rows_val, labels, f, thresholds, bag, subset_fn, max_depth):
+    thr_ptr, thr, n_splits, boz = thresholds
+    tl = [thr[thr_ptr[j]:thr_ptr[j + 1]].tolist() for j in range(f)]
+    rows_bin = [[so.bin_value(tl[j], v) for j, v in zip(ix, vl)] for ix, vl in zip(rows_idx, rows_val)]
+    return so.train_forest(rows_idx, rows_bin, labels.tolist(), tl, boz.tolist(), bag, subset_fn, max_depth)
+
+
+def _same_tree(a, o):
+    assert a.feature.tolist() == o.feature.tolist()
+    assert a.threshold.tolist() == o.threshold.tolist()
+    assert a.left.tolist() == o.left.tolist() and a.right.tolist() == o.right.tolist()
+    assert a.stats.tolist() == o.leaf_value.tolist()
+
+
+def test_find_splits_matches_oracle():
+    rng = np.random.default_rng(3)
+    f = 30
+    feat = rng.integers(0, f, size=4000)
+    val = np.where(feat < 5, np.round(rng.random(4000) * 50, 1), rng.integers(1, 4, size=4000).astype(float))  # feats 0-4: many distinct values
+    val[rng.random(4000) < 0.05] = 0.0
+    feat[feat == 29] = 28  # feature 29 never appears
+    for wns in (1000.0, 260.0):
+        thr_ptr, thr, n_splits, boz = training.find_splits(feat, val, f, wns, 31)
+        for j in range(f):
+            nz = val[(feat == j) & (val != 0.0)]
+            exp = so.find_splits_for_feature(nz.tolist(), wns, 31)
+            assert thr[thr_ptr[j]:thr_ptr[j + 1]].tolist() == exp, j
+            assert n_splits[j] == len(exp) and boz[j] == so.bin_value(exp, 0.0)
+        assert n_splits[29] == 0 and n_splits[:5].max() == 31
+
+
+def test_features_per_node():
+    assert training.features_per_node("auto", 1, 262144) == 262144
+    assert training.features_per_node("auto", 100, 262144) == 512
+    assert training.features_per_node("sqrt", 1, 10000) == 100
+    assert training.features_per_node("log2", 5, 1024) == 10
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from fake_backend import NumpyTreeBackend
+        rows_idx, rows_val, labels, f = _toy()
+        n = len(rows_idx)
+        lo, hi = n * rank // world, n * (rank + 1) // world
+        rng = np.random.default_rng(9)
+        bag = rng.poisson(1.0, size=(3, n)).astype(np.uint8)
+        subsets = {}
+
+        def subset_fn(t, node):
+            return subsets.setdefault((t, node), np.random.default_rng([5, t, node]).permutation(f)[:12].astype(np.int32))
+
+        tr = training.ForestTrainer(NumpyTreeBackend(), f, n_trees=3, max_depth=4, feature_subset_strategy="sqrt", seed=1)
+        rowptr, idx, val = _csr(rows_idx[lo:hi], rows_val[lo:hi])
+        trees = tr.fit(rowptr, idx, val, torch.from_numpy(labels[lo:hi]), bag_weights=torch.from_numpy(bag[:, lo:hi]), subset_fn=subset_fn)
+        # thresholds were found from the all-gathered sample: identical on both ranks, equal to a single-process run
+        _, fi, fv = _csr(rows_idx, rows_val)
+        thresholds = training.find_splits(fi.numpy(), fv.numpy(), f, float(n), min(32, n) - 1)
+        exp = _oracle_forest(rows_idx, rows_val, labels, f, thresholds, bag, subset_fn, 4)
+        for a, o in zip(trees, exp):
+            _same_tree(a, o)
+        assert tr.stats["allreduce_calls"] >= 1 and tr.stats["n_total"] == n
+        out.put((rank, [t.feature.tolist() for t in trees]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_training_grows_the_oracle_trees():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=240)
+        assert p.exitcode == 0
+    got = dict(q.get(timeout=5) for _ in range(2))
+    assert got[0] == got[1] and any(len(t) > 1 for t in got[0])
