@@ -35,6 +35,7 @@ SIGNATURES = {
     "fd_transform": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _p, _p]),
     "fd_status": (C.c_int, [_p, _p]),
     "fd_transform_host": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _p]),
+    "fd_transform_noalloc": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _p, _p, _p]),
     "fd_launch_count": (_i64, [_p]),
     "fd_bin_csr": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p, _p]),
     "fd_rf_histogram": (C.c_int, [_p, _p, _p, _p, _p, _p, _p, _i64, _i32, _p, _p, _p, _i32, _p, _p, _i32, _p, _p]),

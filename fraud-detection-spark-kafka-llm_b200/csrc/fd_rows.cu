@@ -18,6 +18,8 @@
 // Semantics restated from Spark 3.5.5; reference call sites:
 // utils/agent_api.py:143-144 (cleaning), fraud_detection_spark.py:50-53 (Tokenizer, StopWordsRemover,
 // HashingTF/IDF stages), utils/agent_api.py:158-167 (transform + result columns).
+#include <algorithm>
+
 #include "fd_rows.cuh"
 
 namespace fd {
@@ -846,6 +848,41 @@ cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t s
         case MODE_DT: return launch_clean<MODE_DT>(h, a, st);
         case MODE_RF: return launch_clean<MODE_RF>(h, a, st);
         case MODE_GBT: return launch_clean<MODE_GBT>(h, a, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+// Same launch as launch_rows but with a caller-chosen number of wide-table workers (the caller provides
+// a.big_tabs with room for `big_workers` tables).  Used by the entry point that brings its own scratch.
+template <int MODE, bool CLEAN>
+static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a, int big_workers, cudaStream_t st) {
+    const size_t smem = a.m.sw_smem_bytes() + (size_t)ROW_WARPS * sizeof(WarpSmem);
+    const size_t smem_big = a.m.sw_smem_bytes() + sizeof(WarpSmem);
+    auto kern = k_rows<MODE, CLEAN, false>;
+    auto kbig = k_rows<MODE, CLEAN, true>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kbig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_big);
+    if (e != cudaSuccess) return e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, ROW_THREADS, smem);
+    if (e != cudaSuccess) return e;
+    if (occ < 1) occ = 1;
+    long long grid = std::min<long long>((long long)h->sm_count * occ, (a.n_rows + ROW_WARPS - 1) / ROW_WARPS);
+    if (grid < 1) grid = 1;
+    kern<<<(unsigned)grid, ROW_THREADS, smem, st>>>(a);
+    kbig<<<big_workers, 32, smem_big, st>>>(a);
+    h->launches += 2;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int big_workers, cudaStream_t st) {
+    const bool c = (a.flags & FD_FLAG_CLEAN) != 0;
+    switch (mode) {
+        case MODE_LINEAR: return c ? launch_mode_workers<MODE_LINEAR, true>(h, a, big_workers, st) : launch_mode_workers<MODE_LINEAR, false>(h, a, big_workers, st);
+        case MODE_DT: return c ? launch_mode_workers<MODE_DT, true>(h, a, big_workers, st) : launch_mode_workers<MODE_DT, false>(h, a, big_workers, st);
+        case MODE_RF: return c ? launch_mode_workers<MODE_RF, true>(h, a, big_workers, st) : launch_mode_workers<MODE_RF, false>(h, a, big_workers, st);
+        case MODE_GBT: return c ? launch_mode_workers<MODE_GBT, true>(h, a, big_workers, st) : launch_mode_workers<MODE_GBT, false>(h, a, big_workers, st);
     }
     return cudaErrorInvalidValue;
 }

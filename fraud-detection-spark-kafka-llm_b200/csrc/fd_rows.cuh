@@ -49,6 +49,7 @@ __device__ void row_epilogue(const RowArgs& a, WarpSmem& S, unsigned long long* 
                              int lane);
 
 cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st);
+cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int big_workers, cudaStream_t st);
 cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, const unsigned long long* tmp,
                                 long long n_rows, long long* bsum, long long* rowptr, int32_t* out_idx, double* out_val,
                                 bool scan_only, cudaStream_t st);

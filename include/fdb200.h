@@ -125,6 +125,22 @@ int fd_status(fd_handle* h, void* stream);
  * the three result columns are complete in host memory.  text_host needs no padding or alignment. */
 int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* offs_host, int64_t n_rows,
                       uint32_t flags, double* out_pred_host, double* out_prob_host, double* out_raw_host);
+/* No counterpart in the reference (nor in Spark): the fused transform for callers that cannot allocate device
+ * memory -- a host whose GPU memory is already owned by a pool allocator (an inference server, a Spark/RAPIDS
+ * executor), or a latency-bound micro-batch consumer that must not take the driver's allocation lock or hit
+ * an out-of-memory error mid-stream.  Same inputs, outputs and results as fd_transform, but every byte of
+ * scratch lives in a fixed array inside the library image (about 4.5 MiB per GPU, held until the process
+ * exits), so the call performs no cudaMalloc / cudaFree.  Limits and rules:
+ *   - n_rows <= FD_NOALLOC_MAX_ROWS, else FD_ERR_LIMIT and nothing is launched;
+ *   - all calls on one device share the array: calls whose GPU work overlaps race on it -- serialise them;
+ *   - the first call on a device resolves the array's address (once per device): make it before starting any
+ *     stream capture;
+ *   - asynchronous on `stream`; out_status_dev (int32 in device memory, may be NULL) receives FD_OK or
+ *     FD_ERR_LIMIT (a dialogue with more than ~196k distinct hashed terms) when the stream reaches it. */
+#define FD_NOALLOC_MAX_ROWS 65536
+int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev, int64_t n_rows,
+                         uint32_t flags, double* out_pred_dev, double* out_prob_dev, double* out_raw_dev,
+                         int32_t* out_status_dev, void* stream);
 /* Number of kernel launches the handle has issued since creation (bench.py's gpu_launches). */
 int64_t fd_launch_count(fd_handle* h);
 
