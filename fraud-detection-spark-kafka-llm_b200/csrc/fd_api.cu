@@ -93,6 +93,7 @@ int fd_destroy(fd_handle* h) {
     cudaFree(m.nodes);
     cudaFree(m.roots);
     cudaFree(m.leaf2);
+    cudaFree(m.leaf_prob);
     cudaFree(m.tree_w);
     cudaFree(h->ws);
     for (int i = 0; i < 3; ++i) {
@@ -126,11 +127,12 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
         return FD_OK;
     }
     if (n_words > 2048) return set_err(h, FD_ERR_LIMIT, "at most 2048 stop words are supported (got %d)", n_words);
-    int cap = 64;
-    while (cap < 4 * n_words) cap <<= 1;
-    std::vector<uint32_t> tab(cap, 0u);
+    // word records first (duplicates collapse), then a 2-choice cuckoo table over them: every word sits in one of
+    // its two slots (h & mask, (h >> 10) & mask), so a device lookup is two loads and no loop
     std::vector<uint4> wordsv;
+    std::vector<uint32_t> hashes;
     std::vector<uint8_t> pool;
+    std::vector<std::vector<uint8_t>> seen;
     for (int i = 0; i < n_words; ++i) {
         const int len = offs[i + 1] - offs[i];
         if (len < 0) return set_err(h, FD_ERR_INVALID, "stop-word offsets not ascending");
@@ -142,7 +144,11 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
             m.empty_is_stop = 1;
             continue;
         }
-        const uint32_t hsh = murmur3_host(w.data(), len);
+        bool dup = false;
+        for (auto& s0 : seen)
+            if (s0 == w) dup = true;
+        if (dup) continue;
+        seen.push_back(w);
         uint4 s;
         if (len <= 12) {
             uint32_t b[3] = {0, 0, 0};
@@ -152,10 +158,35 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
             s = make_uint4((uint32_t)len | 0x80000000u, (uint32_t)pool.size(), 0, 0);
             pool.insert(pool.end(), w.begin(), w.end());
         }
-        uint32_t slot = hsh & (uint32_t)(cap - 1);
-        while (tab[slot] != 0u) slot = (slot + 1) & (uint32_t)(cap - 1);
-        tab[slot] = (hsh & 0xFFFF0000u) | (uint32_t)(wordsv.size() + 1);
         wordsv.push_back(s);
+        hashes.push_back(murmur3_host(w.data(), len));
+    }
+    int cap = 64;
+    while (cap < 4 * (int)wordsv.size()) cap <<= 1;
+    std::vector<uint32_t> tab;
+    for (;; cap <<= 1) {
+        if (cap > (1 << 16)) return set_err(h, FD_ERR_LIMIT, "could not place the stop words in the lookup table");
+        tab.assign(cap, 0u);
+        const uint32_t mask = (uint32_t)cap - 1u;
+        bool ok = true;
+        for (size_t i = 0; i < wordsv.size() && ok; ++i) {
+            uint32_t id = (uint32_t)i;
+            uint32_t slot = hashes[id] & mask;
+            ok = false;
+            for (int kick = 0; kick < 512; ++kick) {
+                if (tab[slot] == 0u) {
+                    tab[slot] = (hashes[id] & 0xFFFF0000u) | (id + 1u);
+                    ok = true;
+                    break;
+                }
+                const uint32_t other = (tab[slot] & 0xFFFFu) - 1u;  // evict the resident to its alternate slot
+                tab[slot] = (hashes[id] & 0xFFFF0000u) | (id + 1u);
+                id = other;
+                const uint32_t s1 = hashes[id] & mask, s2 = (hashes[id] >> 10) & mask;
+                slot = (slot == s1) ? s2 : s1;
+            }
+        }
+        if (ok) break;
     }
     int rc = upload(h, &m.sw_tab, tab.data(), tab.size());
     if (rc) return rc;
@@ -228,6 +259,7 @@ int fd_set_forest(fd_handle* h, int32_t kind, int32_t n_trees, const int32_t* tr
     const int total = tree_offsets[n_trees];
     std::vector<Node> nodes((size_t)total);
     std::vector<double2> leaf2((size_t)total, make_double2(0.0, 0.0));
+    std::vector<double2> leafp((size_t)total, make_double2(0.0, 0.0));
     std::vector<int32_t> roots((size_t)n_trees);
     std::vector<std::pair<int, int>> queue;
     for (int t = 0; t < n_trees; ++t) {
@@ -248,6 +280,8 @@ int fd_set_forest(fd_handle* h, int32_t kind, int32_t n_trees, const int32_t* tr
                     const double c0 = leaf_value[2 * (size_t)go], c1 = leaf_value[2 * (size_t)go + 1];
                     if (kind == FD_KIND_DT) {
                         leaf2[n] = make_double2(c0, c1);
+                        const double tot = c0 + c1;  // normalizeToProbabilitiesInPlace
+                        leafp[n] = tot != 0.0 ? make_double2(c0 / tot, c1 / tot) : make_double2(c0, c1);
                     } else {  // votes(i) += classCounts(i) / total, skipped when total == 0
                         const double tot = c0 + c1;
                         leaf2[n] = tot != 0.0 ? make_double2(c0 / tot, c1 / tot) : make_double2(0.0, 0.0);
@@ -272,6 +306,7 @@ int fd_set_forest(fd_handle* h, int32_t kind, int32_t n_trees, const int32_t* tr
     Model& m = h->m;
     int rc = upload(h, &m.nodes, nodes.data(), nodes.size());
     if (!rc) rc = upload(h, &m.leaf2, leaf2.data(), leaf2.size());
+    if (!rc) rc = upload(h, &m.leaf_prob, leafp.data(), kind == FD_KIND_DT ? leafp.size() : 0);
     if (!rc) rc = upload(h, &m.roots, roots.data(), roots.size());
     if (!rc && kind == FD_KIND_GBT) rc = upload(h, &m.tree_w, tree_weights, (size_t)n_trees);
     if (rc) return rc;

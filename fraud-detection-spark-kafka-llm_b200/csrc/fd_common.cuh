@@ -34,8 +34,8 @@ struct Ctrl {
 
 struct Model {
     __host__ __device__ size_t sw_smem_bytes() const { return (size_t)sw_cap * 4 + (size_t)n_sw * 16; }
-    // stop words: open-addressed table of 4-byte slots keyed by murmur3(word, 42):
-    //   slot = (hash & 0xFFFF0000) | (word id + 1), 0 = empty; load factor <= 1/4 so most probes end at once
+    // stop words: 2-choice cuckoo table of 4-byte slots keyed by murmur3(word, 42): a word sits at slot
+    //   h & mask or (h >> 10) & mask; slot = (hash & 0xFFFF0000) | (word id + 1), 0 = empty
     uint32_t* sw_tab = nullptr;
     int sw_cap = 0;             // slots, power of two, 0 = no stop words
     uint4* sw_words = nullptr;  // per word: x = len (|0x80000000 when > 12 bytes), y/z/w = first 12 bytes or y = pool offset
@@ -59,6 +59,7 @@ struct Model {
     Node* nodes = nullptr;
     int32_t* roots = nullptr;  // absolute root index per tree
     double2* leaf2 = nullptr;  // DT: raw class stats, RF: stats / total (0,0 when total == 0)
+    double2* leaf_prob = nullptr;  // DT: stats / total, divided once on the host (IEEE division: same bits as on the device)
     double* tree_w = nullptr;
     int n_nodes = 0;
 };

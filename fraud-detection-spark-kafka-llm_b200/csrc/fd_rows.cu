@@ -152,16 +152,15 @@ __device__ __noinline__ bool long_stop_word_equal(const uint8_t* word, const uin
 __device__ bool is_stop_word(const uint32_t* swt, const uint4* sww, int sw_cap, uint32_t h, uint32_t n, uint32_t b0,
                              uint32_t b1, uint32_t b2) {
     const uint32_t mask = (uint32_t)sw_cap - 1u;
-    uint32_t slot = h & mask;
-    for (;;) {
-        const uint32_t e = swt[slot];
-        if (e == 0u) return false;
-        if (((e ^ h) >> 16) == 0u) {
+    const uint32_t cand[2] = {swt[h & mask], swt[(h >> 10) & mask]};
+    for (int i = 0; i < 2; ++i) {
+        const uint32_t e = cand[i];
+        if (e != 0u && ((e ^ h) >> 16) == 0u) {
             const uint4 w = sww[(e & 0xFFFFu) - 1u];
             if (w.x == n && w.y == b0 && w.z == b1 && w.w == b2) return true;
         }
-        slot = (slot + 1u) & mask;
     }
+    return false;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -479,28 +478,21 @@ __global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS, BIG ? 1 : 3) k_rows(co
                     b2 = hs.b2;
                     empty = (n == 0u);
                 }
-                // ---- phase 3: stop-word probe (open addressing keyed by the same hash)
+                // ---- phase 3: stop-word lookup: two candidate slots of the cuckoo table, 16-bit fingerprint, then
+                //      the word record is compared (no loop; the long-word compare is a rare call)
                 bool stop = false;
                 if (m.sw_cap) {
-                    bool probing = valid && !empty;
-                    uint32_t slot = h & swmask;
-                    while (__any_sync(0xFFFFFFFFu, probing)) {
-                        if (probing) {
-                            const uint32_t ent = swt[slot];
-                            if (ent == 0u) {
-                                probing = false;
-                            } else if (((ent ^ h) >> 16) == 0u) {  // 16-bit fingerprint hit: verify the bytes
-                                const uint4 w = sww[(ent & 0xFFFFu) - 1u];
-                                if ((w.x & 0x7FFFFFFFu) == n) {
-                                    const bool same = !(w.x & 0x80000000u) ? (w.y == b0 && w.z == b1 && w.w == b2)
-                                                                           : long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s, e);
-                                    if (same) {
-                                        stop = true;
-                                        probing = false;
-                                    }
-                                }
-                            }
-                            slot = (slot + 1u) & swmask;
+                    const uint32_t e1 = swt[h & swmask], e2 = swt[(h >> 10) & swmask];
+                    const bool m1 = e1 != 0u && ((e1 ^ h) >> 16) == 0u, m2 = e2 != 0u && ((e2 ^ h) >> 16) == 0u;
+                    if (valid && !empty && (m1 || m2)) {
+                        const uint32_t ent = m1 ? e1 : e2;
+                        uint4 w = sww[(ent & 0xFFFFu) - 1u];
+                        stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
+                        if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s, e);
+                        if (!stop && m1 && m2) {  // fingerprint collision in the first slot: look at the second
+                            w = sww[(e2 & 0xFFFFu) - 1u];
+                            stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
+                            if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s, e);
                         }
                     }
                 }
@@ -681,10 +673,8 @@ __device__ void row_epilogue(const RowArgs& a, WarpSmem& S, unsigned long long* 
     } else if (MODE == MODE_DT) {
         Node leaf;
         const int n = walk_tree(m, tab, log2cap, __ldg(m.roots), leaf);
-        const double2 st = __ldg(m.leaf2 + n);
-        const double tot = __dadd_rn(st.x, st.y);
-        const double p0 = tot != 0.0 ? st.x / tot : st.x, p1 = tot != 0.0 ? st.y / tot : st.y;
-        write_result(a, row, lane, st.y > st.x ? 1.0 : 0.0, p0, p1, st.x, st.y);
+        const double2 st = __ldg(m.leaf2 + n), pr = __ldg(m.leaf_prob + n);
+        write_result(a, row, lane, st.y > st.x ? 1.0 : 0.0, pr.x, pr.y, st.x, st.y);
     } else if (MODE == MODE_RF) {
         double v = 0.0;  // lane 0: class 0 votes, lane 1: class 1 votes
         for (int b = 0; b < m.n_trees; b += 32) {

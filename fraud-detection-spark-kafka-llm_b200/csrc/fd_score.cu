@@ -69,12 +69,11 @@ __global__ void __launch_bounds__(256) k_score_csr(const int64_t* __restrict__ r
         } else if (m.kind == FD_KIND_DT) {
             double lp;
             const int nd = walk_csr(m, idx, val, n, __ldg(m.roots), lp);
-            const double2 st = __ldg(m.leaf2 + nd);
-            const double tot = __dadd_rn(st.x, st.y);
+            const double2 st = __ldg(m.leaf2 + nd), pr = __ldg(m.leaf_prob + nd);
             r0 = st.x;
             r1 = st.y;
-            p0 = tot != 0.0 ? st.x / tot : st.x;
-            p1 = tot != 0.0 ? st.y / tot : st.y;
+            p0 = pr.x;
+            p1 = pr.y;
             out_pred = st.y > st.x ? 1.0 : 0.0;
         } else if (m.kind == FD_KIND_RF) {
             double v = 0.0;

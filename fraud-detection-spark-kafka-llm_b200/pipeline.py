@@ -384,7 +384,8 @@ class Pipeline:
         if est:
             c = est[0]
             if isinstance(c, S._TreeEstimator):
-                lab = torch.as_tensor(np.asarray(labels), device=dev).to(torch.uint8)
+                lab = labels if torch.is_tensor(labels) else torch.as_tensor(np.asarray(labels))
+                lab = lab.to(dev).to(torch.uint8)
                 c = c.fit_csr(tf_model.handle(device), rowptr, idx, val, lab, nf, **explicit)
                 c.paramMap.setdefault("featuresCol", fitted[-1].getOrDefault("outputCol"))
             fitted.append(c)
