@@ -25,7 +25,7 @@
 namespace {
 
 constexpr long long NOALLOC_MAX_ROWS = 1 << 16;  // FD_NOALLOC_MAX_ROWS in fdb200.h
-constexpr int NOALLOC_WORKERS = 2;               // wide-table workers (2 MiB table each)
+constexpr int NOALLOC_WORKERS = 8;               // wide-table workers (512 KiB table each)
 constexpr size_t NA_CTRL = 256;
 constexpr size_t NA_TABS = ((size_t)NOALLOC_WORKERS << fd::BIG_LOG2) * 8;
 constexpr size_t NA_LIST = (size_t)NOALLOC_MAX_ROWS * 8;

@@ -163,18 +163,28 @@ __device__ bool is_stop_word(const uint32_t* swt, const uint4* sww, int sw_cap, 
     return false;
 }
 
+// wide-table size for a dialogue of `bytes` bytes: room for every possible token at <= 3/4 load, 2^9 .. 2^BIG_LOG2
+__device__ __forceinline__ int wide_table_log2(long long bytes) {
+    const long long need = (bytes / 2 + 2 + 32) * 2;
+    const int tl = need >= (1LL << BIG_LOG2) ? BIG_LOG2 : 32 - __clz((int)need - 1);
+    return max(tl, 9);
+}
+
 // ------------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------------
-template <int MODE, bool CLEAN, bool BIG>
-__global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS, BIG ? 1 : 3) k_rows(const RowArgs a) {
+template <int MODE, bool CLEAN, bool BIG, int TL>
+__global__ void __launch_bounds__(BIG ? 32 : 32 * row_warps(TL), BIG ? 1 : (TL == 8 ? 2 : 3)) k_rows(const RowArgs a) {
+    constexpr int ROW_WARPS = row_warps(TL);
+    constexpr int TAB_LOG2 = TL;
+    using WarpSmemT = WarpSmem<TL>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint32_t* swt = reinterpret_cast<uint32_t*>(smem_raw);
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const Model& m = a.m;
     uint4* sww = reinterpret_cast<uint4*>(smem_raw + (size_t)m.sw_cap * 4);
-    WarpSmem& S = *reinterpret_cast<WarpSmem*>(smem_raw + m.sw_smem_bytes() + (size_t)warp * sizeof(WarpSmem));
+    WarpSmemT& S = *reinterpret_cast<WarpSmemT*>(smem_raw + m.sw_smem_bytes() + (size_t)warp * sizeof(WarpSmemT));
 
     for (int i = threadIdx.x; i < m.sw_cap; i += blockDim.x) swt[i] = m.sw_tab[i];
     for (int i = threadIdx.x; i < m.n_sw; i += blockDim.x) sww[i] = m.sw_words[i];
@@ -186,15 +196,20 @@ __global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS, BIG ? 1 : 3) k_rows(co
     if (lane < 4) S.lmask[32 + lane] = 0u;
 
     unsigned long long* tab = BIG ? a.big_tabs + ((size_t)blockIdx.x << BIG_LOG2) : S.tab;
-    constexpr int TLOG2 = BIG ? BIG_LOG2 : TAB_LOG2;
-    constexpr int TCAP = 1 << TLOG2;
+    // table size: fixed in shared memory; in the wide-table kernel it follows the dialogue (a dialogue of b bytes
+    // has at most b/2 + 1 tokens), so clearing it costs in proportion to the dialogue, not to the 2^16 maximum
+    int TLOG2 = TAB_LOG2;
     const long long n_items = BIG ? (long long)a.ctrl->big_count : a.n_rows;
     const long long stride = BIG ? (long long)gridDim.x : (long long)gridDim.x * ROW_WARPS;
     long long item = BIG ? (long long)blockIdx.x : (long long)blockIdx.x * ROW_WARPS + warp;
     if (BIG && item >= n_items) return;  // nothing deferred: do not touch the wide table
+    if (BIG) {
+        const long long r0 = a.big_rows[item];
+        TLOG2 = wide_table_log2(a.offs[r0 + 1] - a.offs[r0]);
+    }
     {
         uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);  // count = 0, key = EMPTY
-        for (int i = lane; i < TCAP / 2; i += 32) reinterpret_cast<uint4*>(tab)[i] = ff;
+        for (int i = lane; i < (1 << TLOG2) / 2; i += 32) reinterpret_cast<uint4*>(tab)[i] = ff;
     }
     __syncthreads();
     if (item >= n_items) return;
@@ -416,93 +431,124 @@ __global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS, BIG ? 1 : 3) k_rows(co
             }
             const int t_first = (giant || gt_active) ? 1 : 0;
             const uint32_t swmask = (uint32_t)m.sw_cap - 1u;
-            for (int t0 = t_first; t0 < Tc; t0 += 32) {
-                if (D + 32u > (uint32_t)(TCAP - TCAP / 4)) {  // keep the table at most 3/4 full
+            constexpr int TPL = 1;  // tokens per lane per iteration (2 was measured slower: more idle lanes in the last iteration, 79 registers)
+            for (int t0 = t_first; t0 < Tc; t0 += 32 * TPL) {
+                if (D + 32u * TPL > (3u << TLOG2) / 4u) {  // keep the table at most 3/4 full
                     big = true;
                     break;
                 }
-                // The body is written in warp-uniform phases (boundaries -> hash -> stop-word probe -> insert)
-                // with per-lane predicates instead of nested branches, so the 32 tokens stay in lock step.
-                const int t = t0 + lane;
-                const bool valid = t < Tc;
-                const int tt = valid ? t : t_first;
+                // The body is written in warp-uniform phases (boundaries -> hash -> stop-word lookup -> insert)
+                // with per-lane predicates instead of nested branches, so the 64 tokens stay in lock step.
+                bool valid[TPL], fast[TPL], empty[TPL], slow[TPL];
+                int s[TPL], e[TPL];
+                uint32_t n[TPL], h[TPL], b0[TPL], b1[TPL], b2[TPL];
                 // ---- phase 1: token extent and its kept-byte pattern
-                const int s = S.tok[tt], e = (int)S.tok[tt + 1] - 1;
-                const int len = e - s;
-                const uint32_t bits = __funnelshift_r(S.lmask[s >> 5], S.lmask[(s >> 5) + 1], s & 31) & low_mask(min(len, 32));
-                const int f = __ffs(bits) - 1;  // -1 when no kept byte
-                uint32_t n = (uint32_t)__popc(bits);
-                const bool fast = valid && len <= 32 && bits != 0u && (bits >> (f & 31)) == low_mask((int)n);
-                bool empty = valid && len <= 32 && bits == 0u;
-                const bool slow = valid && !fast && !empty;
+#pragma unroll
+                for (int u = 0; u < TPL; ++u) {
+                    const int t = t0 + 32 * u + lane;
+                    valid[u] = t < Tc;
+                    const int tt = valid[u] ? t : t_first;
+                    s[u] = S.tok[tt];
+                    e[u] = (int)S.tok[tt + 1] - 1;
+                    const int len = e[u] - s[u];
+                    const uint32_t bits = __funnelshift_r(S.lmask[s[u] >> 5], S.lmask[(s[u] >> 5) + 1], s[u] & 31) & low_mask(min(len, 32));
+                    const int f = __ffs(bits) - 1;  // -1 when no kept byte
+                    n[u] = (uint32_t)__popc(bits);
+                    fast[u] = valid[u] && len <= 32 && bits != 0u && (bits >> (f & 31)) == low_mask((int)n[u]);
+                    empty[u] = valid[u] && len <= 32 && bits == 0u;
+                    slow[u] = valid[u] && !fast[u] && !empty[u];
+                    s[u] = fast[u] ? s[u] + f : s[u];  // fast tokens: s now points at the first kept byte
+                }
                 // ---- phase 2: murmur3 of a contiguous token, first 12 bytes straight-line
-                uint32_t h = 42u, b0, b1, b2;
-                {
-                    const int p0 = fast ? s + f : 0;
-                    const int nn = fast ? (int)n : 0;
+                int nn[TPL];
+                bool any_long = false;
+#pragma unroll
+                for (int u = 0; u < TPL; ++u) {
+                    const int p0 = fast[u] ? s[u] : 0;
+                    nn[u] = fast[u] ? (int)n[u] : 0;
                     const uint32_t* wp = reinterpret_cast<const uint32_t*>(rb + (p0 & ~3));
                     const int sh8 = (p0 & 3) * 8;
                     const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
-                    b0 = __funnelshift_r(w0, w1, sh8) & low_mask(8 * max(nn, 0));
-                    b1 = __funnelshift_r(w1, w2, sh8) & low_mask(8 * max(nn - 4, 0));
-                    b2 = __funnelshift_r(w2, w3, sh8) & low_mask(8 * max(nn - 8, 0));
-                    uint32_t kk = mm_k(b0);
-                    h = nn >= 4 ? mm_h(h, kk) : (nn > 0 ? h ^ kk : h);
-                    kk = mm_k(b1);
-                    h = nn >= 8 ? mm_h(h, kk) : (nn > 4 ? h ^ kk : h);
-                    kk = mm_k(b2);
-                    h = nn >= 12 ? mm_h(h, kk) : (nn > 8 ? h ^ kk : h);
-                    if (__any_sync(0xFFFFFFFFu, nn > 12)) {
-                        uint32_t prev = w3;
-                        for (int i = 3; __any_sync(0xFFFFFFFFu, nn > 4 * i); ++i) {
-                            if (nn > 4 * i) {
+                    b0[u] = __funnelshift_r(w0, w1, sh8) & low_mask(8 * nn[u]);
+                    b1[u] = __funnelshift_r(w1, w2, sh8) & low_mask(8 * max(nn[u] - 4, 0));
+                    b2[u] = __funnelshift_r(w2, w3, sh8) & low_mask(8 * max(nn[u] - 8, 0));
+                    uint32_t hh = 42u;
+                    uint32_t kk = mm_k(b0[u]);
+                    hh = nn[u] >= 4 ? mm_h(hh, kk) : (nn[u] > 0 ? hh ^ kk : hh);
+                    kk = mm_k(b1[u]);
+                    hh = nn[u] >= 8 ? mm_h(hh, kk) : (nn[u] > 4 ? hh ^ kk : hh);
+                    kk = mm_k(b2[u]);
+                    hh = nn[u] >= 12 ? mm_h(hh, kk) : (nn[u] > 8 ? hh ^ kk : hh);
+                    h[u] = hh;
+                    any_long |= nn[u] > 12;
+                }
+                if (__any_sync(0xFFFFFFFFu, any_long)) {
+#pragma unroll
+                    for (int u = 0; u < TPL; ++u) {
+                        if (nn[u] > 12) {
+                            const uint32_t* wp = reinterpret_cast<const uint32_t*>(rb + (s[u] & ~3));
+                            const int sh8 = (s[u] & 3) * 8;
+                            uint32_t prev = wp[3];
+                            for (int i = 3; nn[u] > 4 * i; ++i) {
                                 const uint32_t nxt = wp[i + 1];
                                 const uint32_t k = __funnelshift_r(prev, nxt, sh8);
                                 prev = nxt;
-                                const int r = nn - 4 * i;
-                                h = r >= 4 ? mm_h(h, mm_k(k)) : h ^ mm_k(k & low_mask(8 * r));
+                                const int r = nn[u] - 4 * i;
+                                h[u] = r >= 4 ? mm_h(h[u], mm_k(k)) : h[u] ^ mm_k(k & low_mask(8 * r));
                             }
                         }
                     }
-                    h = mm_fmix(h, (uint32_t)nn);
                 }
-                if (slow) {  // kept bytes are not contiguous (or the token is longer than 32 bytes): byte-wise walk
-                    HashState hs;
-                    hs.reset();
-                    for (int p = s; p < e; ++p)
-                        if (letter_at(S.lmask, p)) hs.put(rb[p]);
-                    h = hs.finish();
-                    n = hs.n;
-                    b0 = hs.b0;
-                    b1 = hs.b1;
-                    b2 = hs.b2;
-                    empty = (n == 0u);
+#pragma unroll
+                for (int u = 0; u < TPL; ++u) {
+                    h[u] = mm_fmix(h[u], (uint32_t)nn[u]);
+                    if (slow[u]) {  // kept bytes are not contiguous (or the token is longer than 32 bytes): byte-wise walk
+                        HashState hs;
+                        hs.reset();
+                        for (int p = s[u]; p < e[u]; ++p)
+                            if (letter_at(S.lmask, p)) hs.put(rb[p]);
+                        h[u] = hs.finish();
+                        n[u] = hs.n;
+                        b0[u] = hs.b0;
+                        b1[u] = hs.b1;
+                        b2[u] = hs.b2;
+                        empty[u] = (n[u] == 0u);
+                    }
                 }
                 // ---- phase 3: stop-word lookup: two candidate slots of the cuckoo table, 16-bit fingerprint, then
                 //      the word record is compared (no loop; the long-word compare is a rare call)
-                bool stop = false;
-                if (m.sw_cap) {
-                    const uint32_t e1 = swt[h & swmask], e2 = swt[(h >> 10) & swmask];
-                    const bool m1 = e1 != 0u && ((e1 ^ h) >> 16) == 0u, m2 = e2 != 0u && ((e2 ^ h) >> 16) == 0u;
-                    if (valid && !empty && (m1 || m2)) {
-                        const uint32_t ent = m1 ? e1 : e2;
-                        uint4 w = sww[(ent & 0xFFFFu) - 1u];
-                        stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
-                        if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s, e);
-                        if (!stop && m1 && m2) {  // fingerprint collision in the first slot: look at the second
-                            w = sww[(e2 & 0xFFFFu) - 1u];
-                            stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
-                            if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s, e);
+                bool stop[TPL];
+#pragma unroll
+                for (int u = 0; u < TPL; ++u) {
+                    stop[u] = false;
+                    if (m.sw_cap) {
+                        const uint32_t e1 = swt[h[u] & swmask], e2 = swt[(h[u] >> 10) & swmask];
+                        const bool m1 = e1 != 0u && ((e1 ^ h[u]) >> 16) == 0u, m2 = e2 != 0u && ((e2 ^ h[u]) >> 16) == 0u;
+                        if (valid[u] && !empty[u] && (m1 || m2)) {
+                            const uint32_t ent = m1 ? e1 : e2;
+                            uint4 w = sww[(ent & 0xFFFFu) - 1u];
+                            stop[u] = (w.x == n[u]) && (w.y == b0[u] && w.z == b1[u] && w.w == b2[u]);
+                            if ((w.x & 0x7FFFFFFFu) == n[u] && (w.x & 0x80000000u))
+                                stop[u] = long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s[u], e[u]);
+                            if (!stop[u] && m1 && m2) {  // fingerprint collision in the first slot: look at the second
+                                w = sww[(e2 & 0xFFFFu) - 1u];
+                                stop[u] = (w.x == n[u]) && (w.y == b0[u] && w.z == b1[u] && w.w == b2[u]);
+                                if ((w.x & 0x7FFFFFFFu) == n[u] && (w.x & 0x80000000u))
+                                    stop[u] = long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s[u], e[u]);
+                            }
                         }
                     }
                 }
-                // ---- phase 4: count the surviving token
-                const bool interior_empty = empty && s <= last_letter;
-                const bool ins = valid && (empty ? (interior_empty && !m.empty_is_stop) : !stop);
-                bool isnew = false;
-                if (ins) isnew = tab_insert(tab, TLOG2, empty ? m.empty_idx : feature_index(h, m), 1u, binary);
-                D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
-                pend += __popc(__ballot_sync(0xFFFFFFFFu, empty && !interior_empty));
+                // ---- phase 4: count the surviving tokens
+#pragma unroll
+                for (int u = 0; u < TPL; ++u) {
+                    const bool interior_empty = empty[u] && s[u] <= last_letter;
+                    const bool ins = valid[u] && (empty[u] ? (interior_empty && !m.empty_is_stop) : !stop[u]);
+                    bool isnew = false;
+                    if (ins) isnew = tab_insert(tab, TLOG2, empty[u] ? m.empty_idx : feature_index(h[u], m), 1u, binary);
+                    D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
+                    pend += __popc(__ballot_sync(0xFFFFFFFFu, empty[u] && !interior_empty));
+                }
             }
         }
         gt_active = giant;
@@ -526,13 +572,14 @@ __global__ void __launch_bounds__(BIG ? 32 : ROW_THREADS, BIG ? 1 : 3) k_rows(co
                     else a.ctrl->status = FD_ERR_LIMIT;
                 }
             } else {
-                row_epilogue<MODE>(a, S, tab, TLOG2, row, (int)D, lane);
+                row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), tab, TLOG2, row, (int)D, lane);
             }
             // reset the table and the per-dialogue state
             __syncwarp();
+            if (BIG && have_next) TLOG2 = wide_table_log2(n_end - n_beg);
             {
                 uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);  // count = 0, key = EMPTY
-                for (int i = lane; i < TCAP / 2; i += 32) reinterpret_cast<uint4*>(tab)[i] = ff;
+                for (int i = lane; i < (1 << TLOG2) / 2; i += 32) reinterpret_cast<uint4*>(tab)[i] = ff;
             }
             D = 0;
             pend = 0;
@@ -631,10 +678,9 @@ __device__ __forceinline__ int walk_tree(const Model& m, const unsigned long lon
 }
 
 template <int MODE>
-__device__ void row_epilogue(const RowArgs& a, WarpSmem& S, unsigned long long* tab, int log2cap, long long row, int D,
+__device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long long* tab, int log2cap, long long row, int D,
                              int lane) {
-    const Model& m = a.m;
-    double* scratch = reinterpret_cast<double*>(S.tok);  // 64 doubles of warp scratch (tok is free now)
+    const Model& m = a.m;  // scratch: 64 doubles of warp scratch (the token list, free at this point)
     if (MODE == MODE_CSR) {
         D = compact_and_sort(tab, log2cap, lane);
         unsigned long long pos = 0;
@@ -802,79 +848,51 @@ __global__ void k_gather_csr(const unsigned long long* __restrict__ tmp, const l
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
-template <int MODE, bool CLEAN>
-static cudaError_t launch_mode(fd_handle* h, const RowArgs& a, cudaStream_t st) {
-    const size_t smem = a.m.sw_smem_bytes() + (size_t)ROW_WARPS * sizeof(WarpSmem);
-    const size_t smem_big = a.m.sw_smem_bytes() + sizeof(WarpSmem);
-    auto kern = k_rows<MODE, CLEAN, false>;
-    auto kbig = k_rows<MODE, CLEAN, true>;
+template <int MODE, bool CLEAN, int TL>
+static cudaError_t launch_shape(fd_handle* h, const RowArgs& a, int big_workers, cudaStream_t st) {
+    constexpr int NW = row_warps(TL);
+    const size_t smem = a.m.sw_smem_bytes() + (size_t)NW * sizeof(WarpSmem<TL>);
+    const size_t smem_big = a.m.sw_smem_bytes() + sizeof(WarpSmem<TL>);
+    auto kern = k_rows<MODE, CLEAN, false, TL>;
+    auto kbig = k_rows<MODE, CLEAN, true, TL>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kbig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_big);
     if (e != cudaSuccess) return e;
     int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, ROW_THREADS, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * NW, smem);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
-    long long want = (a.n_rows + ROW_WARPS - 1) / ROW_WARPS;
-    long long grid = (long long)h->sm_count * occ;
-    if (want < grid) grid = want;
+    long long grid = std::min<long long>((long long)h->sm_count * occ, (a.n_rows + NW - 1) / NW);
     if (grid < 1) grid = 1;
-    kern<<<(unsigned)grid, ROW_THREADS, smem, st>>>(a);
-    kbig<<<BIG_WORKERS, 32, smem_big, st>>>(a);
-    h->launches += 2;
-    return cudaGetLastError();
-}
-
-template <int MODE>
-static cudaError_t launch_clean(fd_handle* h, const RowArgs& a, cudaStream_t st) {
-    return (a.flags & FD_FLAG_CLEAN) ? launch_mode<MODE, true>(h, a, st) : launch_mode<MODE, false>(h, a, st);
-}
-
-cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st) {
-    switch (mode) {
-        case MODE_CSR: return launch_clean<MODE_CSR>(h, a, st);
-        case MODE_LINEAR: return launch_clean<MODE_LINEAR>(h, a, st);
-        case MODE_DT: return launch_clean<MODE_DT>(h, a, st);
-        case MODE_RF: return launch_clean<MODE_RF>(h, a, st);
-        case MODE_GBT: return launch_clean<MODE_GBT>(h, a, st);
-    }
-    return cudaErrorInvalidValue;
-}
-
-// Same launch as launch_rows but with a caller-chosen number of wide-table workers (the caller provides
-// a.big_tabs with room for `big_workers` tables).  Used by the entry point that brings its own scratch.
-template <int MODE, bool CLEAN>
-static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a, int big_workers, cudaStream_t st) {
-    const size_t smem = a.m.sw_smem_bytes() + (size_t)ROW_WARPS * sizeof(WarpSmem);
-    const size_t smem_big = a.m.sw_smem_bytes() + sizeof(WarpSmem);
-    auto kern = k_rows<MODE, CLEAN, false>;
-    auto kbig = k_rows<MODE, CLEAN, true>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(kbig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_big);
-    if (e != cudaSuccess) return e;
-    int occ = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, ROW_THREADS, smem);
-    if (e != cudaSuccess) return e;
-    if (occ < 1) occ = 1;
-    long long grid = std::min<long long>((long long)h->sm_count * occ, (a.n_rows + ROW_WARPS - 1) / ROW_WARPS);
-    if (grid < 1) grid = 1;
-    kern<<<(unsigned)grid, ROW_THREADS, smem, st>>>(a);
+    kern<<<(unsigned)grid, 32 * NW, smem, st>>>(a);
     kbig<<<big_workers, 32, smem_big, st>>>(a);
     h->launches += 2;
     return cudaGetLastError();
 }
 
+// big batches: small tables / more warps per SM; micro-batches: larger tables (fewer deferred dialogues)
+template <int MODE, bool CLEAN>
+static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a, int big_workers, cudaStream_t st) {
+    return a.n_rows >= ROWS_FOR_SMALL_TABLES ? launch_shape<MODE, CLEAN, 8>(h, a, big_workers, st)
+                                             : launch_shape<MODE, CLEAN, 9>(h, a, big_workers, st);
+}
+
+// `big_workers` wide-table workers: the caller provides a.big_tabs with room for that many 2^BIG_LOG2-slot tables
 cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int big_workers, cudaStream_t st) {
     const bool c = (a.flags & FD_FLAG_CLEAN) != 0;
     switch (mode) {
+        case MODE_CSR: return c ? launch_mode_workers<MODE_CSR, true>(h, a, big_workers, st) : launch_mode_workers<MODE_CSR, false>(h, a, big_workers, st);
         case MODE_LINEAR: return c ? launch_mode_workers<MODE_LINEAR, true>(h, a, big_workers, st) : launch_mode_workers<MODE_LINEAR, false>(h, a, big_workers, st);
         case MODE_DT: return c ? launch_mode_workers<MODE_DT, true>(h, a, big_workers, st) : launch_mode_workers<MODE_DT, false>(h, a, big_workers, st);
         case MODE_RF: return c ? launch_mode_workers<MODE_RF, true>(h, a, big_workers, st) : launch_mode_workers<MODE_RF, false>(h, a, big_workers, st);
         case MODE_GBT: return c ? launch_mode_workers<MODE_GBT, true>(h, a, big_workers, st) : launch_mode_workers<MODE_GBT, false>(h, a, big_workers, st);
     }
     return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st) {
+    return launch_rows_workers(h, mode, a, BIG_WORKERS, st);
 }
 
 cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, const unsigned long long* tmp,

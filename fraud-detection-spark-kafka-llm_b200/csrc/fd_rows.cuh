@@ -4,24 +4,28 @@
 
 namespace fd {
 
-constexpr int ROW_WARPS = 8;                 // dialogues in flight per CTA
-constexpr int ROW_THREADS = ROW_WARPS * 32;
+// Two shapes of the dialogue kernel, chosen per launch:
+//   TL = 8: 256-slot count tables, 16 warps per CTA -> 32 warps per SM; for large batches, where occupancy pays
+//   TL = 9: 512-slot count tables,  8 warps per CTA -> 24 warps per SM; for micro-batches, where fewer dialogues
+//           overflow into the wide-table kernel (which runs after the main one and would add to the latency)
+__host__ __device__ constexpr int row_warps(int tl) { return tl == 8 ? 16 : 8; }
+constexpr long long ROWS_FOR_SMALL_TABLES = 65536;  // batches at least this large use TL = 8
 constexpr int ROW_CH = 1024;                 // bytes per staged window
 constexpr int ROW_RAWBUF = ROW_CH + 16;      // + slack for word over-reads at the end
-constexpr int TAB_LOG2 = 9;                  // per-warp (bucket -> count) table: 512 slots in shared memory
-constexpr int BIG_LOG2 = 18;                 // wide table (global memory) for dialogues that overflow it
-constexpr int BIG_WORKERS = 16;              // CTAs (one warp each) of the wide-table kernel
+constexpr int BIG_LOG2 = 16;                 // largest wide table (global memory) for dialogues that overflow it
+constexpr int BIG_WORKERS = 148;             // CTAs (one warp each) of the wide-table kernel
 
 enum Mode { MODE_CSR = 0, MODE_LINEAR = 1, MODE_DT = 2, MODE_RF = 3, MODE_GBT = 4 };
 
+template <int TL>
 struct __align__(16) WarpSmem {
     uint8_t raw[2][ROW_RAWBUF];        // TMA-staged windows (double-buffered)
     uint32_t lmask[36];                // letter bitmask of the current window (+ zero tail)
     uint16_t tok[ROW_CH + 8];          // token start offsets of the current window; epilogue scratch
     unsigned long long mbar[2];        // one mbarrier per window buffer
-    unsigned long long tab[1 << TAB_LOG2];  // count in the low word, bucket in the high word
+    unsigned long long tab[1 << TL];   // count in the low word, bucket in the high word
 };
-static_assert(sizeof(WarpSmem) % 16 == 0, "WarpSmem must keep 16-byte alignment");
+static_assert(sizeof(WarpSmem<8>) % 16 == 0 && sizeof(WarpSmem<9>) % 16 == 0, "WarpSmem must keep 16-byte alignment");
 
 struct RowArgs {
     const uint8_t* text;
@@ -45,7 +49,7 @@ struct RowArgs {
 };
 
 template <int MODE>
-__device__ void row_epilogue(const RowArgs& a, WarpSmem& S, unsigned long long* tab, int log2cap, long long row, int D,
+__device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long long* tab, int log2cap, long long row, int D,
                              int lane);
 
 cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st);

@@ -116,7 +116,7 @@ int fd_score(fd_handle* h, const int64_t* rowptr_dev, const int32_t* idx_dev, co
 int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev, int64_t n_rows,
                  uint32_t flags, double* out_pred_dev, double* out_prob_dev, double* out_raw_dev,
                  void* stream);
-/* fd_transform / fd_featurize_* are asynchronous; a dialogue over the size limit (more than ~196k
+/* fd_transform / fd_featurize_* are asynchronous; a dialogue over the size limit (more than ~49k
  * distinct hashed terms) is only detected on the device.  fd_status synchronises `stream` and returns
  * (and clears) that sticky status: FD_OK or FD_ERR_LIMIT. */
 int fd_status(fd_handle* h, void* stream);
@@ -136,7 +136,7 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
  *   - the first call on a device resolves the array's address (once per device): make it before starting any
  *     stream capture;
  *   - asynchronous on `stream`; out_status_dev (int32 in device memory, may be NULL) receives FD_OK or
- *     FD_ERR_LIMIT (a dialogue with more than ~196k distinct hashed terms) when the stream reaches it. */
+ *     FD_ERR_LIMIT (a dialogue with more than ~49k distinct hashed terms) when the stream reaches it. */
 #define FD_NOALLOC_MAX_ROWS 65536
 int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev, int64_t n_rows,
                          uint32_t flags, double* out_pred_dev, double* out_prob_dev, double* out_raw_dev,
