@@ -32,56 +32,70 @@ def find_splits(feat: np.ndarray, val: np.ndarray, n_features: int, weighted_num
     """``RandomForest.findSplitsBySorting`` for continuous features with unit instance weights.
 
     ``feat`` / ``val``: the NON-ZERO entries of the sampled rows.  Returns ``(thr_ptr int32[F+1], thr f64[],
-    n_splits int32[F], bin_of_zero u8[F])``; a feature never seen non-zero in the sample has no split."""
+    n_splits int32[F], bin_of_zero u8[F])``; a feature never seen non-zero in the sample has no split.
+    Vectorised for the usual case (at most ``num_splits`` + 1 distinct values: every midpoint is a threshold);
+    features with more distinct values take Spark's stride walk one by one."""
     feat = np.asarray(feat, dtype=np.int64)
     val = np.asarray(val, dtype=np.float64)
     keep = val != 0.0
     feat, val = feat[keep], val[keep]
-    per_feature: Dict[int, np.ndarray] = {}
-    if feat.size:
-        order = np.lexsort((val, feat))
-        f, v = feat[order], val[order]
-        new = np.ones(f.size, dtype=bool)
-        new[1:] = (f[1:] != f[:-1]) | (v[1:] != v[:-1])
-        starts = np.nonzero(new)[0]
-        uf, uv = f[starts], v[starts]
-        cnt = np.diff(np.append(starts, f.size)).astype(np.float64)
-        fstart = np.nonzero(np.append(True, uf[1:] != uf[:-1]))[0]
-        fend = np.append(fstart[1:], uf.size)
-        for a, b in zip(fstart, fend):
-            fid = int(uf[a])
-            values, counts = uv[a:b], cnt[a:b]
-            part = float(counts.sum())
-            tol = EPSILON * part * 100
-            if weighted_num_samples - part > tol:  # add the implied zero-valued rows
-                pos = int(np.searchsorted(values, 0.0))
-                values = np.insert(values, pos, 0.0)
-                counts = np.insert(counts, pos, weighted_num_samples - part)
-            possible = values.size - 1
-            if possible == 0:
-                continue
-            if possible <= num_splits:
-                per_feature[fid] = (values[:-1] + values[1:]) / 2.0
-                continue
-            stride = weighted_num_samples / (num_splits + 1)
-            out = []
-            current = counts[0]
-            target = stride
-            for i in range(1, values.size):
-                previous = current
-                current = current + counts[i]
-                if abs(previous - target) < abs(current - target):
-                    out.append((values[i - 1] + values[i]) / 2.0)
-                    target += stride
-            if out:
-                per_feature[fid] = np.asarray(out, dtype=np.float64)
     n_splits = np.zeros(n_features, dtype=np.int32)
+    bin_of_zero = np.zeros(n_features, dtype=np.uint8)
+    thr_ptr = np.zeros(n_features + 1, dtype=np.int32)
+    if feat.size == 0:
+        return thr_ptr, np.zeros(0, dtype=np.float64), n_splits, bin_of_zero
+    # distinct (feature, value) pairs with their counts
+    order = np.lexsort((val, feat))
+    f, v = feat[order], val[order]
+    new = np.ones(f.size, dtype=bool)
+    new[1:] = (f[1:] != f[:-1]) | (v[1:] != v[:-1])
+    starts = np.nonzero(new)[0]
+    uf, uv = f[starts], v[starts]
+    cnt = np.diff(np.append(starts, f.size)).astype(np.float64)
+    fstart = np.nonzero(np.append(True, uf[1:] != uf[:-1]))[0]
+    fids = uf[fstart]
+    part = np.add.reduceat(cnt, fstart)
+    # the implied zero-valued rows of each feature
+    need_zero = (weighted_num_samples - part) > (EPSILON * part * 100)
+    af = np.concatenate([uf, fids[need_zero]])
+    av = np.concatenate([uv, np.zeros(int(need_zero.sum()))])
+    ac = np.concatenate([cnt, weighted_num_samples - part[need_zero]])
+    order = np.lexsort((av, af))
+    af, av, ac = af[order], av[order], ac[order]
+    gstart = np.nonzero(np.append(True, af[1:] != af[:-1]))[0]
+    gsize = np.diff(np.append(gstart, af.size))
+    gf = af[gstart]
+    possible = gsize - 1
+    same = np.zeros(af.size, dtype=bool)
+    same[1:] = af[1:] == af[:-1]
+    mids = np.zeros(af.size)
+    mids[1:] = (av[:-1] + av[1:]) / 2.0
+    simple = np.repeat(possible <= num_splits, gsize) & same      # midpoint rows of the simple features
+    per_feature: Dict[int, np.ndarray] = {}
+    for gi in np.nonzero(possible > num_splits)[0]:                # Spark's stride walk for the others
+        a0, b0 = gstart[gi], gstart[gi] + gsize[gi]
+        values, counts = av[a0:b0], ac[a0:b0]
+        stride = weighted_num_samples / (num_splits + 1)
+        out = []
+        current = counts[0]
+        target = stride
+        for i in range(1, values.size):
+            previous = current
+            current = current + counts[i]
+            if abs(previous - target) < abs(current - target):
+                out.append((values[i - 1] + values[i]) / 2.0)
+                target += stride
+        per_feature[int(gf[gi])] = np.asarray(out, dtype=np.float64)
+    np.add.at(n_splits, af[simple], 1)
     for fid, t in per_feature.items():
         n_splits[fid] = t.size
-    thr_ptr = np.zeros(n_features + 1, dtype=np.int32)
     np.cumsum(n_splits, out=thr_ptr[1:])
     thr = np.zeros(int(thr_ptr[-1]), dtype=np.float64)
-    bin_of_zero = np.zeros(n_features, dtype=np.uint8)
+    sf_, sm_ = af[simple], mids[simple]                            # already ordered by (feature, value)
+    first = np.nonzero(np.append(True, sf_[1:] != sf_[:-1]))[0] if sf_.size else np.zeros(0, dtype=np.int64)
+    within = np.arange(sf_.size) - np.repeat(first, np.diff(np.append(first, sf_.size))) if sf_.size else np.zeros(0, dtype=np.int64)
+    thr[thr_ptr[sf_] + within] = sm_
+    np.add.at(bin_of_zero, sf_[sm_ < 0.0], 1)                      # lower_bound(thresholds, 0.0)
     for fid, t in per_feature.items():
         thr[thr_ptr[fid]:thr_ptr[fid + 1]] = t
         bin_of_zero[fid] = int(np.searchsorted(t, 0.0, side="left"))
@@ -139,6 +153,43 @@ def default_subset_fn(seed: int, n_features: int, k: int) -> Callable[[int, int]
         return out[:k].astype(np.int32)
 
     return fn
+
+
+def default_subset_batch(seed: int, n_features: int, k: int, device):
+    """Default subsets for a whole node group at once, drawn ON THE DEVICE: ``fn(depth, first, m) -> int64 [m, k]``
+    (k distinct features per node, in order of first appearance).  Every rank calls it with the same arguments
+    and the same seeded generator, so the subsets agree across ranks without any exchange."""
+    import torch
+
+    def fn(depth: int, first: int, m: int):
+        if k >= n_features:
+            return torch.arange(n_features, device=device).expand(m, n_features)
+        g = torch.Generator(device=device)
+        g.manual_seed(((seed & 0x7FFFFFFF) * 1000003 + depth * 7919 + first) & 0x7FFFFFFFFFFFFFFF)
+        width = int(k * 1.15) + 16
+        while True:
+            draws = torch.randint(0, n_features, (m, width), generator=g, device=device)
+            srt, order = torch.sort(draws, dim=1, stable=True)
+            dup_sorted = torch.zeros_like(draws, dtype=torch.bool)
+            dup_sorted[:, 1:] = srt[:, 1:] == srt[:, :-1]
+            dup = torch.zeros_like(dup_sorted).scatter_(1, order, dup_sorted)  # later occurrences are the duplicates
+            keep = ~dup
+            keep &= torch.cumsum(keep, dim=1) <= k
+            if bool((keep.sum(dim=1) == k).all()):
+                return draws[keep].view(m, k)
+            width *= 2  # vanishingly rare: some node drew fewer than k distinct features
+
+    return fn
+
+
+def _units_device(col_len, feats):
+    """Device version of :func:`_units`."""
+    import torch
+    nseg = (col_len[feats] + SEG_LEN - 1) // SEG_LEN
+    unit_item = torch.repeat_interleave(torch.arange(feats.numel(), dtype=torch.int32, device=feats.device), nseg)
+    first = torch.cumsum(nseg, 0) - nseg
+    unit_seg = (torch.arange(unit_item.numel(), dtype=torch.int64, device=feats.device) - torch.repeat_interleave(first, nseg)).to(torch.int32)
+    return unit_item, unit_seg
 
 
 # ------------------------------------------------------------------------------------------ backend
@@ -224,6 +275,17 @@ class ForestTrainer:
         self.min_instances, self.min_info_gain = int(min_instances_per_node), float(min_info_gain)
         self.strategy, self.rate, self.seed, self.prune = feature_subset_strategy, float(subsampling_rate), int(seed), bool(prune)
         self.stats: Dict[str, float] = {}
+        self.profile = False  # when set, phases are timed with a device synchronise on both sides (slower)
+        self._t: Dict[str, float] = {}
+
+    def _tick(self, name: str, t0: float) -> float:
+        import time
+        if self.profile:
+            self.b.torch.cuda.synchronize() if hasattr(self.b, "torch") else None
+            now = time.perf_counter()
+            self._t[name] = self._t.get(name, 0.0) + now - t0
+            return now
+        return t0
 
     # -- thresholds from a row sample gathered over ranks
     def _thresholds(self, rowptr, idx, val, n_total: int, rank: int):
@@ -264,7 +326,11 @@ class ForestTrainer:
             dist.all_reduce(nt)
         n_total = int(nt.item())
         # ---- thresholds, bins, CSC
+        import time
+        self._t = {}
+        tt = self._tick("start", time.perf_counter())
         thr_ptr, thr, n_splits, bin_of_zero = thresholds if thresholds is not None else self._thresholds(rowptr, idx, val, n_total, rank)
+        tt = self._tick("thresholds", tt)
         d_thr_ptr = torch.from_numpy(thr_ptr).to(dev)
         d_thr = torch.from_numpy(thr).to(dev)
         d_nsplits = torch.from_numpy(n_splits).to(dev)
@@ -277,6 +343,7 @@ class ForestTrainer:
         torch.cumsum(torch.bincount(idx.long(), minlength=self.F), 0, out=csc[0][1:])
         col_len = np.diff(csc[0].cpu().numpy())
         del order, row_of, bins
+        tt = self._tick("bin+csc", tt)
         labels = labels.to(dev).to(torch.uint8).contiguous()
         # ---- bagging
         if bag_weights is None:
@@ -295,7 +362,9 @@ class ForestTrainer:
             dist.all_reduce(root)
         root = root.cpu().numpy()
         k = features_per_node(self.strategy, self.T, self.F)
-        subset_fn = subset_fn or default_subset_fn(self.seed, self.F, k)
+        batch_fn = default_subset_batch(self.seed, self.F, k, dev) if subset_fn is None else None
+        d_col_len = csc[0][1:] - csc[0][:-1]
+        tt = self._tick("bagging+root", tt)
         # ---- level-wise growth; nodes[t][heap id] = record
         nodes: List[Dict[int, dict]] = [{1: {"stats": [float(root[t, 0]), float(root[t, 1])], "leaf": True}} for t in range(self.T)]
         frontier = [(t, 1) for t in range(self.T)]
@@ -309,39 +378,56 @@ class ForestTrainer:
             next_frontier = []
             g0 = 0
             while g0 < len(active):
-                # ---- one node group: items (node x feature subset, features without thresholds dropped)
-                it_t, it_n, it_f, ptr = [], [], [], [0]
+                # ---- one node group: items = node x feature subset (features without thresholds dropped), on the device
                 g1 = g0
-                while g1 < len(active) and (g1 == g0 or ptr[-1] < MAX_ITEMS_PER_GROUP):
-                    t, n = active[g1]
-                    feats = np.asarray(subset_fn(t, n), dtype=np.int32)
-                    feats = feats[n_splits[feats] > 0]
-                    it_t.append(np.full(feats.size, t, np.int32))
-                    it_n.append(np.full(feats.size, n, np.int32))
-                    it_f.append(feats)
-                    ptr.append(ptr[-1] + feats.size)
-                    g1 += 1
+                if batch_fn is not None:
+                    per_node = max(1, min(k, self.F))
+                    g1 = min(len(active), g0 + max(1, MAX_ITEMS_PER_GROUP // per_node))
+                    grp = torch.tensor(active[g0:g1], dtype=torch.int32, device=dev)
+                    sub = batch_fn(depth, g0, g1 - g0)                           # [m, k]
+                    ok = d_nsplits[sub] > 0
+                    cnt = ok.sum(dim=1)
+                    items = (torch.repeat_interleave(grp[:, 0], cnt), torch.repeat_interleave(grp[:, 1], cnt), sub[ok].to(torch.int32))
+                    d_ptr = torch.zeros(g1 - g0 + 1, dtype=torch.int32, device=dev)
+                    d_ptr[1:] = torch.cumsum(cnt, 0)
+                else:
+                    it_t, it_n, it_f, ptr = [], [], [], [0]
+                    while g1 < len(active) and (g1 == g0 or ptr[-1] < MAX_ITEMS_PER_GROUP):
+                        t, n = active[g1]
+                        feats = np.asarray(subset_fn(t, n), dtype=np.int32)
+                        feats = feats[n_splits[feats] > 0]
+                        it_t.append(np.full(feats.size, t, np.int32))
+                        it_n.append(np.full(feats.size, n, np.int32))
+                        it_f.append(feats)
+                        ptr.append(ptr[-1] + feats.size)
+                        g1 += 1
+                    items = tuple(torch.from_numpy(np.concatenate(x)).to(dev) for x in (it_t, it_n, it_f))
+                    d_ptr = torch.tensor(ptr, dtype=torch.int32, device=dev)
                 group = active[g0:g1]
                 g0 = g1
-                f_all = np.concatenate(it_f) if it_f else np.zeros(0, np.int32)
-                if f_all.size == 0:
+                tt = self._tick("subsets+items", tt)
+                if items[2].numel() == 0:
                     continue
-                items = tuple(torch.from_numpy(np.concatenate(a)).to(dev) for a in (it_t, it_n, it_f))
-                units = tuple(torch.from_numpy(a).to(dev) for a in _units(col_len, f_all))
+                units = _units_device(d_col_len, items[2].long())
+                tt = self._tick("units", tt)
                 hist = self.b.histogram(csc, labels, bagw, node_id, items, units)
+                tt = self._tick("kernel:histogram", tt)
                 if dist is not None and dist.get_world_size() > 1:
                     dist.all_reduce(hist)  # integer counts: exact, order-independent
                     allreduce_calls += 1
                 hist_bytes += hist.numel() * 4
+                tt = self._tick("allreduce", tt)
                 totals = torch.tensor([nodes[t][n]["stats"] for (t, n) in group], dtype=torch.float64, device=dev)
-                bi, bs, bg, left, right = self.b.best_split(hist, torch.tensor(ptr, dtype=torch.int32, device=dev), items[2], totals,
-                                                            d_nsplits, d_bz, self.min_instances, self.min_info_gain)
-                bi, bs, bg, left, right = (x.cpu().numpy() for x in (bi, bs, bg, left, right))
+                bi, bs, bg, left, right = self.b.best_split(hist, d_ptr, items[2], totals, d_nsplits, d_bz, self.min_instances,
+                                                            self.min_info_gain)
+                bf = items[2][bi.clamp(min=0).long()]  # feature of the winning item
+                bi, bs, bg, left, right, bf = (x.cpu().numpy() for x in (bi, bs, bg, left, right, bf))
                 del hist
+                tt = self._tick("kernel:best_split+d2h", tt)
                 for j, (t, n) in enumerate(group):
                     if bi[j] < 0 or not (bg[j] > 0.0):
                         continue  # stays a leaf
-                    f = int(f_all[bi[j]])
+                    f = int(bf[j])
                     sb = int(bs[j])
                     rec = nodes[t][n]
                     rec.update(leaf=False, feature=f, split_bin=sb, threshold=float(thr[thr_ptr[f] + sb]), gain=float(bg[j]))
@@ -349,6 +435,7 @@ class ForestTrainer:
                     nodes[t][2 * n + 1] = {"stats": [float(right[j, 0]), float(right[j, 1])], "leaf": True}
                     splits.append((t, n, f, sb))
                     next_frontier += [(t, 2 * n), (t, 2 * n + 1)]
+            tt = self._tick("host:grow", tt)
             if not splits:
                 break
             sp = np.asarray(splits, dtype=np.int32)
@@ -358,7 +445,8 @@ class ForestTrainer:
             units = tuple(torch.from_numpy(a).to(dev) for a in _units(col_len, sp[:, 2]))
             self.b.advance(csc, node_id, base, d_sp, units, torch.from_numpy(action).to(dev))
             frontier = next_frontier
-        self.stats = {"hist_bytes": float(hist_bytes), "allreduce_calls": float(allreduce_calls), "n_total": float(n_total)}
+            tt = self._tick("kernel:advance", tt)
+        self.stats = {"phases_s": dict(self._t), "hist_bytes": float(hist_bytes), "allreduce_calls": float(allreduce_calls), "n_total": float(n_total)}
         return [self._to_tree(nd) for nd in nodes]
 
     # -- LearningNode.toNode(prune): heap-indexed records -> pre-order arrays

@@ -57,6 +57,7 @@ def main():
     ap.add_argument("--train-rows", type=int, default=1_000_000)
     ap.add_argument("--train-trees", type=int, default=20)
     ap.add_argument("--train-depth", type=int, default=6)
+    ap.add_argument("--train-profile", action="store_true")
     a = ap.parse_args()
     import torch.distributed as dist
     world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
@@ -150,6 +151,14 @@ def main():
         pipe = fd.Pipeline(stages=st + [fd.IDF(inputCol="raw_features", outputCol="features"),
                                         fd.RandomForestClassifier(featuresCol="features", labelCol="labels", numTrees=a.train_trees,
                                                                   maxDepth=a.train_depth, seed=42, featureSubsetStrategy="auto")])
+        if a.train_profile:
+            import importlib as _il
+            _tr = _il.import_module("fraud-detection-spark-kafka-llm_b200.training")
+            _orig = _tr.ForestTrainer.__init__
+            def _init(self, *aa, **kw):
+                _orig(self, *aa, **kw)
+                self.profile = True
+            _tr.ForestTrainer.__init__ = _init
         model = pipe.fit(pk, labels=lab)
         torch.cuda.synchronize(dev)
         secs = maxreduce(time.perf_counter() - t0)

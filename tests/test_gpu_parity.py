@@ -67,6 +67,25 @@ def test_featurize_messy_text_bit_exact(fd, num_features, binary):
             assert vl == evl, repr(t)
 
 
+@pytest.mark.parametrize("case_sensitive", [False, True])
+def test_custom_stop_word_lists(fd, case_sensitive):
+    """Stop words longer than 12 bytes (byte-compared from the pool), an empty-string stop word, mixed case and a
+    few hundred entries (cuckoo placement) -- against the oracle."""
+    rng = np.random.default_rng(3)
+    many = ["w" + "".join(chr(97 + int(c)) for c in rng.integers(0, 26, size=int(rng.integers(1, 16)))) for _ in range(600)]
+    words = ["the", "Hello", "antidisestablishmentarianism", "internationalisation", "", "social", "xx", "q"] + many
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"),
+              fd.StopWordsRemover(inputCol="words", outputCol="filtered", stopWords=words, caseSensitive=case_sensitive),
+              fd.HashingTF(inputCol="filtered", outputCol="features", numFeatures=4096)]
+    model = fd.PipelineModel(stages)
+    texts = messy_texts(400, seed=12) + [" ".join(many[:300]) + " keep me", "a  b   antidisestablishmentarianism internationalisations"]
+    ora = oracle_for(model)
+    rowptr, idx, val = model.featurize(texts)
+    for t, (ix, vl) in zip(texts, csr_rows(rowptr, idx, val)):
+        eix, evl, _, _ = ora.featurize(t.encode())
+        assert ix == eix and vl == evl, repr(t[:50])
+
+
 def _long_rows():
     rng = np.random.default_rng(11)
     words = [bytes(rng.integers(97, 123, size=int(rng.integers(1, 9)), dtype=np.uint8)).decode() for _ in range(5000)]
