@@ -257,7 +257,8 @@ def main():
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         with open(tp) as f:
-            traffic = json.load(f).get("k_rows_dt_clean_bytes_per_launch")
+            per_dialogue = json.load(f).get("k_rows_dt_clean_bytes_per_dialogue")
+            traffic = None if per_dialogue is None else per_dialogue * n  # DRAM bytes of one launch over this batch
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f64",
            "data": "synthetic",

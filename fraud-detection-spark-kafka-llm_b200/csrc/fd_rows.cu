@@ -186,6 +186,7 @@ __global__ void __launch_bounds__(BIG ? 32 : 32 * row_warps(TL), BIG ? 1 : (TL =
     uint4* sww = reinterpret_cast<uint4*>(smem_raw + (size_t)m.sw_cap * 4);
     WarpSmemT& S = *reinterpret_cast<WarpSmemT*>(smem_raw + m.sw_smem_bytes() + (size_t)warp * sizeof(WarpSmemT));
 
+    if (BIG && (long long)blockIdx.x >= (long long)a.ctrl->big_count) return;  // nothing deferred to this worker
     for (int i = threadIdx.x; i < m.sw_cap; i += blockDim.x) swt[i] = m.sw_tab[i];
     for (int i = threadIdx.x; i < m.n_sw; i += blockDim.x) sww[i] = m.sw_words[i];
     if (lane == 0) {
