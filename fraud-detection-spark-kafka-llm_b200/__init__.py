@@ -5,8 +5,10 @@ random-forest histogram training.  The directory name is not a Python identifier
 module at the repository root."""
 from . import spark_format
 from ._lib import FdError, Handle, LIB_PATH, load_library
+from .evaluation import BinaryClassificationEvaluator, MulticlassClassificationEvaluator, confusion_matrix
 from .packing import PackedText, pack_strings
 from .pipeline import Pipeline, PipelineModel, Row, TransformResult, predict_and_get_label
+from .serving import MicroBatcher, classify_batch
 from .stages import (DecisionTreeClassificationModel, DecisionTreeClassifier, RandomForestClassifier, GBTClassificationModel, HashingTF, IDF, IDFModel,
                      LogisticRegressionModel, RandomForestClassificationModel, StopWordsRemover, Tokenizer,
                      load_default_stop_words, load_stage)

@@ -619,6 +619,60 @@ def _heap_to_tree(nodes: dict, n_classes: int, prune: bool) -> Tree:
 
 
 # ---------------------------------------------------------------------------------------------
+# evaluators   (mllib BinaryClassificationMetrics / MulticlassMetrics)   reference: fraud_detection_spark.py:101-119
+# ---------------------------------------------------------------------------------------------
+def area_under_roc(scores: Sequence[float], labels: Sequence[float], num_bins: int = 1000) -> float:
+    """``BinaryClassificationMetrics(scoreAndLabels, numBins).areaUnderROC`` on ONE partition: counts per distinct
+    score (descending), optional down-sampling in chunks of ``distinct // numBins``, ROC points with (0,0) and
+    (1,1) added, trapezoid rule summed left to right."""
+    counts = {}
+    for s, y in zip(scores, labels):
+        c = counts.setdefault(float(s), [0.0, 0.0])
+        c[0 if y > 0.5 else 1] += 1.0
+    items = [(s, counts[s]) for s in sorted(counts, reverse=True)]
+    grouping = len(items) // num_bins if num_bins > 0 else 0
+    if grouping >= 2:
+        binned = []
+        for i in range(0, len(items), grouping):
+            chunk = items[i:i + grouping]
+            binned.append((chunk[-1][0], [sum(c[1][0] for c in chunk), sum(c[1][1] for c in chunk)]))
+        items = binned
+    tot_p = sum(c[0] for _, c in items)
+    tot_n = sum(c[1] for _, c in items)
+    pts = [(0.0, 0.0)]
+    cp = cn = 0.0
+    for _, c in items:
+        cp += c[0]
+        cn += c[1]
+        pts.append((cn / tot_n if tot_n > 0 else 0.0, cp / tot_p if tot_p > 0 else 0.0))
+    pts.append((1.0, 1.0))
+    area = 0.0
+    for (x0, y0), (x1, y1) in zip(pts[:-1], pts[1:]):
+        area += (x1 - x0) * (y1 + y0) / 2.0
+    return area
+
+
+def multiclass_metrics(labels: Sequence[float], predictions: Sequence[float]) -> dict:
+    """``MulticlassMetrics``: accuracy, weightedPrecision, weightedRecall, weightedFMeasure(beta = 1)."""
+    classes = sorted(set(float(y) for y in labels))
+    n = float(len(labels))
+    out = {"accuracy": sum(1.0 for y, p in zip(labels, predictions) if y == p) / n, "weightedPrecision": 0.0,
+           "weightedRecall": 0.0, "f1": 0.0}
+    for c in classes:
+        tp = sum(1.0 for y, p in zip(labels, predictions) if y == c and p == c)
+        fp = sum(1.0 for y, p in zip(labels, predictions) if y != c and p == c)
+        cnt = sum(1.0 for y in labels if y == c)
+        prec = tp / (tp + fp) if tp + fp > 0 else 0.0
+        rec = tp / cnt if cnt > 0 else 0.0
+        f = 2.0 * prec * rec / (prec + rec) if prec + rec > 0 else 0.0
+        w = cnt / n
+        out["weightedPrecision"] += prec * w
+        out["weightedRecall"] += rec * w
+        out["f1"] += f * w
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
 # convenience: a whole pipeline over a batch (used by tests and the golden generator)
 # ---------------------------------------------------------------------------------------------
 class OraclePipeline:

@@ -177,3 +177,89 @@ def test_empty_batch_and_errors(fd, shipped_model_dir):
     h = fd.Handle(0)
     with pytest.raises(fd.FdError):
         h.call("fd_transform", None, None, 1, 1, None, None, None, None)
+
+
+def test_random_byte_strings_property(fd, shipped_model_dir):
+    """Property test (hypothesis): arbitrary valid-UTF-8 dialogues -- control characters, every kind of white space,
+    astral code points, lone combining marks -- give the oracle's indices, counts and margins bit for bit, in both
+    the cleaning mode and the Tokenizer-only mode."""
+    from hypothesis import HealthCheck, given, settings, strategies as st
+
+    model = fd.PipelineModel.load(shipped_model_dir)
+    ora = oracle_for(model)
+    alphabet = st.one_of(st.sampled_from(list(" \t\n\x0b\x0c\r .,'!-aAbBzZiIkK09İKſß")), st.characters(blacklist_categories=("Cs",)))
+    texts = st.lists(st.text(alphabet=alphabet, max_size=300), min_size=1, max_size=40)
+
+    @settings(max_examples=25, deadline=None, suppress_health_check=list(HealthCheck))
+    @given(texts)
+    def run(batch):
+        rowptr, idx, val = model.featurize(batch)
+        for t, (ix, vl) in zip(batch, csr_rows(rowptr, idx, val)):
+            eix, evl, _, _ = ora.featurize(t.encode("utf-8"))
+            assert ix == eix and vl == evl, repr(t)
+        exp = ora.transform([t.encode("utf-8") for t in batch])
+        _check_scores(model.transform(batch), exp)
+        ascii_only = [t for t in batch if t.isascii()]
+        if ascii_only:  # Tokenizer-only mode (the kernel folds ASCII case; the host folds the rest)
+            rowptr, idx, val = model.featurize(ascii_only, cleaned=True)
+            for t, (ix, vl) in zip(ascii_only, csr_rows(rowptr, idx, val)):
+                eix, evl, _, _ = ora.featurize(t.encode(), do_clean=False)
+                assert ix == eix and vl == evl, repr(t)
+
+    run()
+
+
+def test_micro_batcher_and_batch_classification(fd, shipped_model_dir, golden):
+    """Kafka-shaped loop (app_ui.py:195-226) and CSV batch loop (app_ui.py:144-150) as ONE transform per batch."""
+    import json
+
+    class Msg:
+        def __init__(self, key, value, err=None):
+            self._k, self._v, self._e = key, value, err
+
+        def key(self):
+            return self._k
+
+        def value(self):
+            return self._v
+
+        def error(self):
+            return self._e
+
+    class Consumer:
+        def __init__(self, msgs):
+            self.q = list(msgs)
+
+        def poll(self, timeout):
+            return self.q.pop(0) if self.q else None
+
+    class Producer:
+        def __init__(self):
+            self.sent, self.flushes = [], 0
+
+        def produce(self, topic, key, value):
+            self.sent.append((topic, key, json.loads(value)))
+
+        def flush(self):
+            self.flushes += 1
+
+    model = fd.PipelineModel.load(shipped_model_dir)
+    recs = golden["provisional_oracle_outputs"]
+    msgs = [Msg(str(i).encode(), json.dumps({"text": r["text"]}).encode()) for i, r in enumerate(recs)]
+    msgs.insert(3, Msg(b"bad", b"not json"))
+    errors = []
+    prod = Producer()
+    mb = fd.MicroBatcher(model, Consumer(msgs), prod, "out-topic", max_batch=8, max_wait_s=1.0, on_error=errors.append)
+    out = []
+    while True:
+        got = mb.step()
+        if not got:
+            break
+        out += got
+    assert len(out) == len(recs) and len(errors) == 1 and mb.batches == 2 and prod.flushes == 2
+    for o, r, sent in zip(out, recs, prod.sent):
+        assert o["prediction"] == r["prediction"] and abs(o["confidence"] - r["probability"][1]) <= 1e-9 * r["probability"][1]
+        assert sent[0] == "out-topic" and sent[2]["original_text"] == r["text"] and sent[2]["prediction"] == r["prediction"]
+    rows = fd.classify_batch(model, [r["text"] for r in recs])
+    assert [x["prediction"] for x in rows] == [r["prediction"] for r in recs]
+    assert rows[5]["predicted_label"] == "Potentially Fraudulent"
