@@ -7,18 +7,19 @@
 
 namespace fd {
 
-constexpr size_t SLOT_CTRL = 256;
-constexpr size_t SLOT_BIGTABS = ((size_t)BIG_WORKERS << BIG_LOG2) * 8;
-constexpr long long BIG_LIST_CAP = 1 << 16;
-constexpr size_t SLOT_FIXED = SLOT_CTRL + SLOT_BIGTABS + (size_t)BIG_LIST_CAP * 8;
-
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-static void fill_slot(RowArgs& a, char* base) {
+constexpr size_t SLOT_CTRL = 256;
+constexpr size_t SLOT_BIGTABS = ((size_t)BIG_WORKERS << BIG_LOG2) * 8;
+// scratch slot = control block, wide tables, then the deferred-dialogue list with ONE ENTRY PER DIALOGUE of the
+// call (every dialogue may be deferred, so the list can never overflow)
+static size_t slot_bytes(long long n_rows) { return align_up(SLOT_CTRL + SLOT_BIGTABS + (size_t)n_rows * 8, 256); }
+
+static void fill_slot(RowArgs& a, char* base, long long n_rows) {
     a.ctrl = reinterpret_cast<Ctrl*>(base);
     a.big_tabs = reinterpret_cast<unsigned long long*>(base + SLOT_CTRL);
     a.big_rows = reinterpret_cast<long long*>(base + SLOT_CTRL + SLOT_BIGTABS);
-    a.big_cap = BIG_LIST_CAP;
+    a.big_cap = n_rows;
 }
 
 static int classifier_mode(fd_handle* h, int* mode) {
@@ -51,7 +52,7 @@ static int run_featurize_pass(fd_handle* h, const uint8_t* text, const int64_t* 
                               int64_t tmp_cap, cudaStream_t st, Ctrl* result) {
     // workspace: [slot fixed][row_nnz i32][row_tmpoff i64][bsum i64][tmp u64]
     const size_t nb = (size_t)((n_rows + 1023) / 1024);
-    const size_t off_nnz = SLOT_FIXED;
+    const size_t off_nnz = slot_bytes(n_rows);
     const size_t off_tmpoff = align_up(off_nnz + (size_t)n_rows * 4, 256);
     const size_t off_bsum = align_up(off_tmpoff + (size_t)n_rows * 8, 256);
     const size_t off_tmp = align_up(off_bsum + (nb + 1) * 8, 256);
@@ -70,7 +71,7 @@ static int run_featurize_pass(fd_handle* h, const uint8_t* text, const int64_t* 
     a.n_rows = n_rows;
     a.flags = flags;
     a.m = h->m;
-    fill_slot(a, h->ws);
+    fill_slot(a, h->ws, n_rows);
     a.row_nnz = reinterpret_cast<int32_t*>(h->ws + off_nnz);
     a.row_tmpoff = reinterpret_cast<long long*>(h->ws + off_tmpoff);
     a.tmp = reinterpret_cast<unsigned long long*>(h->ws + off_tmp);
@@ -183,7 +184,7 @@ int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev,
     if (!out_pred_dev || !out_prob_dev || !out_raw_dev) return set_err(h, FD_ERR_INVALID, "null output column");
     FD_CUDA(h, cudaSetDevice(h->device));
     cudaStream_t st = (cudaStream_t)stream;
-    rc = ensure_ws(h, SLOT_FIXED);
+    rc = ensure_ws(h, slot_bytes(n_rows));
     if (rc) return rc;
     RowArgs a;
     memset(&a, 0, sizeof(a));
@@ -192,7 +193,7 @@ int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev,
     a.n_rows = n_rows;
     a.flags = flags;
     a.m = h->m;
-    fill_slot(a, h->ws);
+    fill_slot(a, h->ws, n_rows);
     a.pred = out_pred_dev;
     a.prob = out_prob_dev;
     a.raw = out_raw_dev;
@@ -247,7 +248,7 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
         const int64_t nr = r1 - r0, b0 = offs_host[r0], nbytes = offs_host[r1] - b0;
         const int s = c % 3;
         const size_t d = (size_t)(b0 & 15);
-        const size_t off_text = SLOT_FIXED;
+        const size_t off_text = slot_bytes(nr);
         const size_t off_offs = align_up(off_text + d + (size_t)nbytes + 32, 256);
         const size_t off_pred = align_up(off_offs + (size_t)(nr + 1) * 8, 256);
         const size_t off_prob = off_pred + (size_t)nr * 8;
@@ -259,7 +260,7 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
                 FD_CUDA(h, cudaFree(h->hbuf[s]));
                 h->hbuf[s] = nullptr;
             }
-            const size_t sz = std::max(need, SLOT_FIXED + (size_t)CHUNK_BYTES + (size_t)CHUNK_ROWS * 48 + 4096);
+            const size_t sz = std::max(need, slot_bytes(CHUNK_ROWS) + (size_t)CHUNK_BYTES + (size_t)CHUNK_ROWS * 48 + 4096);
             FD_CUDA(h, cudaMalloc((void**)&h->hbuf[s], sz));
             h->hbuf_bytes[s] = sz;
             FD_CUDA(h, cudaMemsetAsync(h->hbuf[s], 0, 256, h->hs[s]));
@@ -268,7 +269,7 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
         cudaStream_t st = h->hs[s];
         RowArgs a;
         memset(&a, 0, sizeof(a));
-        fill_slot(a, base);
+        fill_slot(a, base, nr);
         if (nbytes > 0)
             FD_CUDA(h, cudaMemcpyAsync(base + off_text + d, text_host + b0, (size_t)nbytes, cudaMemcpyHostToDevice, st));
         FD_CUDA(h, cudaMemcpyAsync(base + off_offs, offs_host + r0, (size_t)(nr + 1) * 8, cudaMemcpyHostToDevice, st));

@@ -263,3 +263,25 @@ def test_micro_batcher_and_batch_classification(fd, shipped_model_dir, golden):
     rows = fd.classify_batch(model, [r["text"] for r in recs])
     assert [x["prediction"] for x in rows] == [r["prediction"] for r in recs]
     assert rows[5]["predicted_label"] == "Potentially Fraudulent"
+
+
+def test_many_deferred_dialogues_at_scale(fd):
+    """70,000 dialogues that ALL overflow the in-shared-memory count table (about 190 distinct buckets each): every
+    one goes through the wide-table kernel and its per-call deferred list.  Checked against the C port of the oracle
+    (itself proven equal to the Python oracle in tests/test_oracle_c.py)."""
+    from oracle import c_oracle
+    model, corpus = _tree_model(fd, "rf", 12, 6)
+    rng = np.random.default_rng(21)
+    vocab = np.array([("w" + "".join(chr(97 + c) for c in rng.integers(0, 26, size=5))).encode() for _ in range(6000)], dtype=object)
+    n = 70000
+    rows = [b" ".join(vocab[rng.integers(0, 6000, size=200)]) for _ in range(n)]
+    pk = fd.PackedText.from_strings(rows)
+    res = model.transform(pk, cleaned=False)
+    o = oracle_for(model)
+    co = c_oracle.COracle(model._plan.stop.getOrDefault("stopWords"), False, o.num_features, o.binary, o.idf, o.classifier)
+    pred, prob, raw = co.transform(pk.data, pk.offs, True)
+    _check_scores(res, (pred, prob, raw))
+    rowptr, idx, val = model.featurize(pk, cleaned=False)
+    rp, ix, vl = co.featurize(pk.data, pk.offs, True)
+    assert np.array_equal(rowptr.cpu().numpy(), rp) and np.array_equal(idx.cpu().numpy(), ix) and np.array_equal(val.cpu().numpy(), vl)
+    assert (np.diff(rp) > 160).mean() > 0.99
