@@ -102,6 +102,84 @@ def find_splits(feat: np.ndarray, val: np.ndarray, n_features: int, weighted_num
     return thr_ptr, thr, n_splits, bin_of_zero
 
 
+def find_splits_torch(feat, val, n_features: int, weighted_num_samples: float, num_splits: int):
+    """:func:`find_splits` with the sorting and grouping done by torch on the tensors' device (the sampled entries
+    never leave the GPU); only features with more than ``num_splits`` + 1 distinct values are walked on the host.
+    Returns the same four numpy arrays."""
+    import torch
+    dev = feat.device
+    keep = val != 0.0
+    f, v = feat[keep].long(), val[keep].to(torch.float64)
+    n_splits = torch.zeros(n_features, dtype=torch.int64, device=dev)
+    boz = torch.zeros(n_features, dtype=torch.int64, device=dev)
+    if f.numel() == 0:
+        return (np.zeros(n_features + 1, np.int32), np.zeros(0, np.float64), np.zeros(n_features, np.int32), np.zeros(n_features, np.uint8))
+
+    def sort_fv(ff, vv, *rest):
+        o = torch.argsort(vv, stable=True)
+        ff, vv, rest = ff[o], vv[o], [r[o] for r in rest]
+        o = torch.argsort(ff, stable=True)
+        return (ff[o], vv[o], *[r[o] for r in rest])
+
+    f, v = sort_fv(f, v)
+    new = torch.ones(f.numel(), dtype=torch.bool, device=dev)
+    new[1:] = (f[1:] != f[:-1]) | (v[1:] != v[:-1])
+    starts = torch.nonzero(new).flatten()
+    uf, uv = f[starts], v[starts]
+    cnt = torch.diff(torch.cat([starts, torch.tensor([f.numel()], device=dev)])).to(torch.float64)
+    fnew = torch.ones(uf.numel(), dtype=torch.bool, device=dev)
+    fnew[1:] = uf[1:] != uf[:-1]
+    gid = torch.cumsum(fnew, 0) - 1
+    fids = uf[fnew]
+    part = torch.zeros(fids.numel(), dtype=torch.float64, device=dev).index_add_(0, gid, cnt)
+    need_zero = (weighted_num_samples - part) > (EPSILON * part * 100)
+    af = torch.cat([uf, fids[need_zero]])
+    av = torch.cat([uv, torch.zeros(int(need_zero.sum()), dtype=torch.float64, device=dev)])
+    ac = torch.cat([cnt, weighted_num_samples - part[need_zero]])
+    af, av, ac = sort_fv(af, av, ac)
+    gnew = torch.ones(af.numel(), dtype=torch.bool, device=dev)
+    gnew[1:] = af[1:] != af[:-1]
+    g2 = torch.cumsum(gnew, 0) - 1
+    gstart = torch.nonzero(gnew).flatten()
+    gsize = torch.bincount(g2)
+    possible = gsize - 1
+    mids = torch.zeros(af.numel(), dtype=torch.float64, device=dev)
+    mids[1:] = (av[:-1] + av[1:]) / 2.0
+    simple = (possible <= num_splits)[g2] & ~gnew                      # midpoint rows of the simple features
+    n_splits.index_add_(0, af[simple], torch.ones(int(simple.sum()), dtype=torch.int64, device=dev))
+    hard = {}
+    for gi in torch.nonzero(possible > num_splits).flatten().tolist():    # Spark's stride walk, on the host
+        a0, b0 = int(gstart[gi]), int(gstart[gi] + gsize[gi])
+        values, counts = av[a0:b0].cpu().numpy(), ac[a0:b0].cpu().numpy()
+        stride = weighted_num_samples / (num_splits + 1)
+        out, current, target = [], counts[0], stride
+        for i in range(1, values.size):
+            previous = current
+            current = current + counts[i]
+            if abs(previous - target) < abs(current - target):
+                out.append((values[i - 1] + values[i]) / 2.0)
+                target += stride
+        hard[int(af[a0])] = np.asarray(out, dtype=np.float64)
+        n_splits[int(af[a0])] = len(out)
+    thr_ptr = torch.zeros(n_features + 1, dtype=torch.int64, device=dev)
+    thr_ptr[1:] = torch.cumsum(n_splits, 0)
+    thr = torch.zeros(int(thr_ptr[-1]), dtype=torch.float64, device=dev)
+    sf_, sm_ = af[simple], mids[simple]
+    if sf_.numel():
+        first = torch.ones(sf_.numel(), dtype=torch.bool, device=dev)
+        first[1:] = sf_[1:] != sf_[:-1]
+        fpos = torch.nonzero(first).flatten()
+        within = torch.arange(sf_.numel(), device=dev) - fpos[torch.cumsum(first, 0) - 1]
+        thr[thr_ptr[sf_] + within] = sm_
+        boz.index_add_(0, sf_[sm_ < 0.0], torch.ones(int((sm_ < 0.0).sum()), dtype=torch.int64, device=dev))
+    thr_ptr_np = thr_ptr.cpu().numpy().astype(np.int32)
+    thr_np, ns_np, boz_np = thr.cpu().numpy(), n_splits.cpu().numpy().astype(np.int32), boz.cpu().numpy().astype(np.uint8)
+    for fid, t in hard.items():
+        thr_np[thr_ptr_np[fid]:thr_ptr_np[fid + 1]] = t
+        boz_np[fid] = int(np.searchsorted(t, 0.0, side="left"))
+    return thr_ptr_np, thr_np, ns_np, boz_np
+
+
 def gini(counts: Sequence[float]) -> float:
     total = 0.0
     for c in counts:
@@ -303,14 +381,25 @@ class ForestTrainer:
             counts = rowptr[1:] - rowptr[:-1]
             mask = torch.repeat_interleave(pick, counts)
             sel_f, sel_v = idx[mask], val[mask]
-        f_np, v_np = sel_f.cpu().numpy(), sel_v.cpu().numpy()
         if dist is not None and dist.get_world_size() > 1:
-            parts: List = [None] * dist.get_world_size()
-            dist.all_gather_object(parts, (f_np, v_np))
-            f_np = np.concatenate([p[0] for p in parts])
-            v_np = np.concatenate([p[1] for p in parts])
+            # every rank needs the SAME sample: all-gather the sampled entries (padded to the longest shard)
+            ws = dist.get_world_size()
+            n_loc = torch.tensor([sel_f.numel()], dtype=torch.int64, device=sel_f.device)
+            sizes = [torch.zeros_like(n_loc) for _ in range(ws)]
+            dist.all_gather(sizes, n_loc)
+            mx = int(max(int(x.item()) for x in sizes))
+            pf = torch.zeros(mx, dtype=torch.int32, device=sel_f.device)
+            pv = torch.zeros(mx, dtype=torch.float64, device=sel_f.device)
+            pf[:sel_f.numel()] = sel_f
+            pv[:sel_v.numel()] = sel_v
+            gf = [torch.empty_like(pf) for _ in range(ws)]
+            gv = [torch.empty_like(pv) for _ in range(ws)]
+            dist.all_gather(gf, pf)
+            dist.all_gather(gv, pv)
+            sel_f = torch.cat([g[:int(n.item())] for g, n in zip(gf, sizes)])
+            sel_v = torch.cat([g[:int(n.item())] for g, n in zip(gv, sizes)])
         num_splits = min(self.max_bins, n_total) - 1
-        return find_splits(f_np, v_np, self.F, fraction * n_total, num_splits)
+        return find_splits_torch(sel_f, sel_v, self.F, fraction * n_total, num_splits)
 
     def fit(self, rowptr, idx, val, labels, bag_weights=None, subset_fn=None, thresholds=None) -> List[sf.TreeArrays]:
         """``rowptr/idx/val``: this rank's CSR rows (torch tensors on the backend device); ``labels`` uint8.

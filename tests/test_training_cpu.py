@@ -65,6 +65,9 @@ def test_find_splits_matches_oracle():
             assert thr[thr_ptr[j]:thr_ptr[j + 1]].tolist() == exp, j
             assert n_splits[j] == len(exp) and boz[j] == so.bin_value(exp, 0.0)
         assert n_splits[29] == 0 and n_splits[:5].max() == 31
+        dev = training.find_splits_torch(torch.from_numpy(feat.astype(np.int32)), torch.from_numpy(val), f, wns, 31)
+        for x, y in zip((thr_ptr, thr, n_splits, boz), dev):   # the device-side version gives the same arrays
+            assert np.array_equal(x, y)
 
 
 def test_features_per_node():
