@@ -289,27 +289,44 @@ def main():
 
 
 def stage_times(model, pk, dev, stats):
-    """featurize -> CSR and CSR -> score timed separately (3 repetitions each after one warm-up)."""
+    """featurize -> CSR and CSR -> score timed separately through the C-ABI with preallocated outputs
+    (3 repetitions each after one warm-up)."""
     import torch
     res = {}
     n = pk.n_rows
+    h = model.handle(dev.index)
+    P = lambda t: C.c_void_p(t.data_ptr())
+    sp = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     rowptr, idx, val = model.featurize(pk, cleaned=False)
+    nnz = int(idx.numel())
+    cnt = C.c_int64(0)
+
+    def feat():
+        h.call("fd_featurize", P(pk.data), P(pk.offs), n, 1, P(rowptr), P(idx), P(val), nnz, C.byref(cnt), sp)
+
+    feat()
     torch.cuda.synchronize(dev)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(3):
-        rowptr, idx, val = model.featurize(pk, cleaned=False)
+        feat()
     e1.record()
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1) / 3
-    nnz = int(idx.numel())
     b = stats["text_bytes"] + 8 * n + 12 * nnz + 8 * n
     res["featurize_csr"] = {"ms": ms, "dialogues_per_s": n / ms * 1e3, "algorithmic_GBps": b / ms / 1e6, "nnz": nnz}
-    model.score(rowptr, idx, val)
+    pred = torch.empty(n, dtype=torch.float64, device=dev)
+    prob = torch.empty((n, 2), dtype=torch.float64, device=dev)
+    raw = torch.empty((n, 2), dtype=torch.float64, device=dev)
+
+    def score():
+        h.call("fd_score", P(rowptr), P(idx), P(val), n, P(pred), P(prob), P(raw), sp)
+
+    score()
     torch.cuda.synchronize(dev)
     e0.record()
     for _ in range(3):
-        model.score(rowptr, idx, val)
+        score()
     e1.record()
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1) / 3

@@ -10,7 +10,7 @@ namespace fd {
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 constexpr size_t SLOT_CTRL = 256;
-constexpr size_t SLOT_BIGTABS = ((size_t)BIG_WORKERS << BIG_LOG2) * 8;
+constexpr size_t SLOT_BIGTABS = wide_pool_slots(MED_CTAS, BIG_WORKERS) * 8;
 // scratch slot = control block, wide tables, then the deferred-dialogue list with ONE ENTRY PER DIALOGUE of the
 // call (every dialogue may be deferred, so the list can never overflow)
 static size_t slot_bytes(long long n_rows) { return align_up(SLOT_CTRL + SLOT_BIGTABS + (size_t)n_rows * 8, 256); }
@@ -76,7 +76,7 @@ static int run_featurize_pass(fd_handle* h, const uint8_t* text, const int64_t* 
     a.row_tmpoff = reinterpret_cast<long long*>(h->ws + off_tmpoff);
     a.tmp = reinterpret_cast<unsigned long long*>(h->ws + off_tmp);
     a.tmp_cap = tmp_cap;
-    FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, 16, st));  // cursor, big_count, overflow (status is sticky)
+    FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, CTRL_CLEAR_BYTES, st));  // cursor, big_count, overflow (status is sticky)
     FD_CUDA(h, launch_rows(h, MODE_CSR, a, st));
     return read_ctrl(h, a.ctrl, result, st);
 }
@@ -197,7 +197,7 @@ int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev,
     a.pred = out_pred_dev;
     a.prob = out_prob_dev;
     a.raw = out_raw_dev;
-    FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, 16, st));
+    FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, CTRL_CLEAR_BYTES, st));
     FD_CUDA(h, launch_rows(h, mode, a, st));
     return FD_OK;
 }
@@ -281,7 +281,7 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
         a.pred = reinterpret_cast<double*>(base + off_pred);
         a.prob = reinterpret_cast<double*>(base + off_prob);
         a.raw = reinterpret_cast<double*>(base + off_raw);
-        FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, 16, st));
+        FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, CTRL_CLEAR_BYTES, st));
         FD_CUDA(h, launch_rows(h, mode, a, st));
         FD_CUDA(h, cudaMemcpyAsync(out_pred_host + r0, a.pred, (size_t)nr * 8, cudaMemcpyDeviceToHost, st));
         FD_CUDA(h, cudaMemcpyAsync(out_prob_host + 2 * r0, a.prob, (size_t)nr * 16, cudaMemcpyDeviceToHost, st));

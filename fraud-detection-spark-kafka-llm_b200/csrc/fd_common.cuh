@@ -24,12 +24,14 @@ struct __align__(16) Node {
 constexpr uint32_t EMPTY_KEY = 0xFFFFFFFFu;
 
 // control block at the start of the workspace (device memory, written by kernels)
+constexpr size_t CTRL_CLEAR_BYTES = 20;  // tmp_cursor, big_count, big2_count, tmp_overflow
 struct Ctrl {
     unsigned long long tmp_cursor;  // entries allocated in the CSR staging buffer
-    unsigned int big_count;         // dialogues deferred to the wide-table kernel
+    unsigned int big_count;         // dialogues deferred to the medium wide-table kernel (list grows from the front)
+    unsigned int big2_count;        // dialogues deferred to the large wide-table kernel (list grows from the back)
     unsigned int tmp_overflow;      // staging buffer was too small
-    int status;                     // sticky device-side status (FD_OK / FD_ERR_LIMIT)
-    unsigned int pad[3];
+    int status;                     // sticky device-side status (FD_OK / FD_ERR_LIMIT); NOT cleared per call
+    unsigned int pad[2];
 };
 
 struct Model {

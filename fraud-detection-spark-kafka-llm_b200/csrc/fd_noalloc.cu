@@ -25,9 +25,10 @@
 namespace {
 
 constexpr long long NOALLOC_MAX_ROWS = 1 << 16;  // FD_NOALLOC_MAX_ROWS in fdb200.h
-constexpr int NOALLOC_WORKERS = 8;               // wide-table workers (512 KiB table each)
+constexpr int NOALLOC_WORKERS = 8;               // large wide-table workers (512 KiB table each)
+constexpr int NOALLOC_MED_CTAS = 16;             // medium wide-table CTAs (8 warps x 32 KiB each); shares the same 4 MiB
 constexpr size_t NA_CTRL = 256;
-constexpr size_t NA_TABS = ((size_t)NOALLOC_WORKERS << fd::BIG_LOG2) * 8;
+constexpr size_t NA_TABS = fd::wide_pool_slots(NOALLOC_MED_CTAS, NOALLOC_WORKERS) * 8;
 constexpr size_t NA_LIST = (size_t)NOALLOC_MAX_ROWS * 8;
 constexpr size_t NA_BYTES = NA_CTRL + NA_TABS + NA_LIST;
 
@@ -95,7 +96,7 @@ extern "C" int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const
     a.raw = out_raw_dev;
     // the array still holds the previous call's counters and status: they must start at zero
     FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, sizeof(Ctrl), st));
-    if (n_rows > 0) FD_CUDA(h, launch_rows_workers(h, mode, a, NOALLOC_WORKERS, st));
+    if (n_rows > 0) FD_CUDA(h, launch_rows_workers(h, mode, a, NOALLOC_MED_CTAS, NOALLOC_WORKERS, st));
     if (out_status_dev)
         FD_CUDA(h, cudaMemcpyAsync(out_status_dev, &a.ctrl->status, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
     return FD_OK;

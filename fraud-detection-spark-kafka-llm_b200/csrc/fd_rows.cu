@@ -166,16 +166,18 @@ __device__ bool is_stop_word(const uint32_t* swt, const uint4* sww, int sw_cap, 
 // wide-table size for a dialogue of `bytes` bytes: room for every possible token at <= 3/4 load, 2^9 .. 2^BIG_LOG2
 __device__ __forceinline__ int wide_table_log2(long long bytes) {
     const long long need = (bytes / 2 + 2 + 32) * 2;
-    const int tl = need >= (1LL << BIG_LOG2) ? BIG_LOG2 : 32 - __clz((int)need - 1);
+    const int tl = need >= (1LL << BIG_LOG2) ? BIG_LOG2 : 32 - __clz((int)need - 1);  // ceil(log2(need))
     return max(tl, 9);
 }
 
 // ------------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------------
-template <int MODE, bool CLEAN, bool BIG, int TL>
-__global__ void __launch_bounds__(BIG ? 32 : 32 * row_warps(TL), BIG ? 1 : (TL == 8 ? 2 : 3)) k_rows(const RowArgs a) {
-    constexpr int ROW_WARPS = row_warps(TL);
+// BIG = 0: main kernel (count table in shared memory); 1: medium wide tables (8 warps per CTA); 2: large wide tables
+template <int MODE, bool CLEAN, int BIG, int TL>
+__global__ void __launch_bounds__(BIG == 2 ? 32 : (BIG == 1 ? 32 * MED_WARPS : 32 * row_warps(TL)), BIG ? 1 : (TL == 8 ? 2 : 3))
+k_rows(const RowArgs a) {
+    constexpr int ROW_WARPS = BIG == 2 ? 1 : (BIG == 1 ? MED_WARPS : row_warps(TL));
     constexpr int TAB_LOG2 = TL;
     using WarpSmemT = WarpSmem<TL>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -186,7 +188,8 @@ __global__ void __launch_bounds__(BIG ? 32 : 32 * row_warps(TL), BIG ? 1 : (TL =
     uint4* sww = reinterpret_cast<uint4*>(smem_raw + (size_t)m.sw_cap * 4);
     WarpSmemT& S = *reinterpret_cast<WarpSmemT*>(smem_raw + m.sw_smem_bytes() + (size_t)warp * sizeof(WarpSmemT));
 
-    if (BIG && (long long)blockIdx.x >= (long long)a.ctrl->big_count) return;  // nothing deferred to this worker
+    if (BIG && (long long)blockIdx.x * ROW_WARPS >= (long long)(BIG == 1 ? a.ctrl->big_count : a.ctrl->big2_count))
+        return;  // nothing deferred to this CTA
     for (int i = threadIdx.x; i < m.sw_cap; i += blockDim.x) swt[i] = m.sw_tab[i];
     for (int i = threadIdx.x; i < m.n_sw; i += blockDim.x) sww[i] = m.sw_words[i];
     if (lane == 0) {
@@ -196,16 +199,18 @@ __global__ void __launch_bounds__(BIG ? 32 : 32 * row_warps(TL), BIG ? 1 : (TL =
     }
     if (lane < 4) S.lmask[32 + lane] = 0u;
 
-    unsigned long long* tab = BIG ? a.big_tabs + ((size_t)blockIdx.x << BIG_LOG2) : S.tab;
+    unsigned long long* tab = BIG == 1 ? a.big_tabs + ((size_t)(blockIdx.x * MED_WARPS + warp) << MED_LOG2)
+                            : (BIG == 2 ? a.big_tabs + ((size_t)blockIdx.x << BIG_LOG2) : S.tab);
     // table size: fixed in shared memory; in the wide-table kernel it follows the dialogue (a dialogue of b bytes
     // has at most b/2 + 1 tokens), so clearing it costs in proportion to the dialogue, not to the 2^16 maximum
     int TLOG2 = TAB_LOG2;
-    const long long n_items = BIG ? (long long)a.ctrl->big_count : a.n_rows;
-    const long long stride = BIG ? (long long)gridDim.x : (long long)gridDim.x * ROW_WARPS;
-    long long item = BIG ? (long long)blockIdx.x : (long long)blockIdx.x * ROW_WARPS + warp;
-    if (BIG && item >= n_items) return;  // nothing deferred: do not touch the wide table
-    if (BIG) {
-        const long long r0 = a.big_rows[item];
+    const long long n_items = BIG == 1 ? (long long)a.ctrl->big_count : (BIG == 2 ? (long long)a.ctrl->big2_count : a.n_rows);
+    const long long stride = (long long)gridDim.x * ROW_WARPS;
+    long long item = (long long)blockIdx.x * ROW_WARPS + warp;
+    // deferred lists: medium dialogues from the front of big_rows, large ones from its back
+    auto deferred_row = [&](long long i) { return BIG == 1 ? a.big_rows[i] : a.big_rows[a.big_cap - 1 - i]; };
+    if (BIG && item < n_items) {
+        const long long r0 = deferred_row(item);
         TLOG2 = wide_table_log2(a.offs[r0 + 1] - a.offs[r0]);
     }
     {
@@ -219,7 +224,7 @@ __global__ void __launch_bounds__(BIG ? 32 : 32 * row_warps(TL), BIG ? 1 : (TL =
     const bool binary = m.binary != 0;
 
     // ---- window bookkeeping (all warp-uniform) ----
-    long long row = BIG ? a.big_rows[item] : item;
+    long long row = BIG ? deferred_row(item) : item;
     long long row_beg = a.offs[row], row_end = a.offs[row + 1];
     long long wbase = row_beg & ~15LL;             // global byte offset of buffer byte 0
     int lo = (int)(row_beg - wbase);               // first valid byte of the window
@@ -368,7 +373,7 @@ __global__ void __launch_bounds__(BIG ? 32 : 32 * row_warps(TL), BIG ? 1 : (TL =
             n_item = item + stride;
             have_next = n_item < n_items;
             if (have_next) {
-                n_row = BIG ? a.big_rows[n_item] : n_item;
+                n_row = BIG ? deferred_row(n_item) : n_item;
                 n_beg = a.offs[n_row];
                 n_end = a.offs[n_row + 1];
             }
@@ -568,9 +573,14 @@ __global__ void __launch_bounds__(BIG ? 32 : 32 * row_warps(TL), BIG ? 1 : (TL =
                 if (BIG) {
                     if (lane == 0) a.ctrl->status = FD_ERR_LIMIT;
                 } else if (lane == 0) {
-                    const unsigned int pos = atomicAdd(&a.ctrl->big_count, 1u);
-                    if ((long long)pos < a.big_cap) a.big_rows[pos] = row;
-                    else a.ctrl->status = FD_ERR_LIMIT;
+                    // size class by the table the dialogue can need at most
+                    if (wide_table_log2(row_end - row_beg) <= MED_LOG2) {
+                        const unsigned int pos = atomicAdd(&a.ctrl->big_count, 1u);
+                        a.big_rows[pos] = row;
+                    } else {
+                        const unsigned int pos = atomicAdd(&a.ctrl->big2_count, 1u);
+                        a.big_rows[a.big_cap - 1 - pos] = row;
+                    }
                 }
             } else {
                 row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), tab, TLOG2, row, (int)D, lane);
@@ -850,13 +860,17 @@ __global__ void k_gather_csr(const unsigned long long* __restrict__ tmp, const l
 // launchers
 // ------------------------------------------------------------------------------------------------
 template <int MODE, bool CLEAN, int TL>
-static cudaError_t launch_shape(fd_handle* h, const RowArgs& a, int big_workers, cudaStream_t st) {
+static cudaError_t launch_shape(fd_handle* h, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st) {
     constexpr int NW = row_warps(TL);
     const size_t smem = a.m.sw_smem_bytes() + (size_t)NW * sizeof(WarpSmem<TL>);
+    const size_t smem_med = a.m.sw_smem_bytes() + (size_t)MED_WARPS * sizeof(WarpSmem<TL>);
     const size_t smem_big = a.m.sw_smem_bytes() + sizeof(WarpSmem<TL>);
-    auto kern = k_rows<MODE, CLEAN, false, TL>;
-    auto kbig = k_rows<MODE, CLEAN, true, TL>;
+    auto kern = k_rows<MODE, CLEAN, 0, TL>;
+    auto kmed = k_rows<MODE, CLEAN, 1, TL>;
+    auto kbig = k_rows<MODE, CLEAN, 2, TL>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kmed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_med);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(kbig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_big);
     if (e != cudaSuccess) return e;
@@ -867,33 +881,36 @@ static cudaError_t launch_shape(fd_handle* h, const RowArgs& a, int big_workers,
     long long grid = std::min<long long>((long long)h->sm_count * occ, (a.n_rows + NW - 1) / NW);
     if (grid < 1) grid = 1;
     kern<<<(unsigned)grid, 32 * NW, smem, st>>>(a);
+    kmed<<<med_ctas, 32 * MED_WARPS, smem_med, st>>>(a);
     kbig<<<big_workers, 32, smem_big, st>>>(a);
-    h->launches += 2;
+    h->launches += 3;
     return cudaGetLastError();
 }
 
 // big batches: small tables / more warps per SM; micro-batches: larger tables (fewer deferred dialogues)
 template <int MODE, bool CLEAN>
-static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a, int big_workers, cudaStream_t st) {
-    return a.n_rows >= ROWS_FOR_SMALL_TABLES ? launch_shape<MODE, CLEAN, 8>(h, a, big_workers, st)
-                                             : launch_shape<MODE, CLEAN, 9>(h, a, big_workers, st);
+static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st) {
+    return a.n_rows >= ROWS_FOR_SMALL_TABLES ? launch_shape<MODE, CLEAN, 8>(h, a, med_ctas, big_workers, st)
+                                             : launch_shape<MODE, CLEAN, 9>(h, a, med_ctas, big_workers, st);
 }
 
-// `big_workers` wide-table workers: the caller provides a.big_tabs with room for that many 2^BIG_LOG2-slot tables
-cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int big_workers, cudaStream_t st) {
+// the caller provides a.big_tabs with wide_pool_slots(med_ctas, big_workers) slots
+cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st) {
     const bool c = (a.flags & FD_FLAG_CLEAN) != 0;
+#define FD_DISPATCH(M) return c ? launch_mode_workers<M, true>(h, a, med_ctas, big_workers, st) : launch_mode_workers<M, false>(h, a, med_ctas, big_workers, st)
     switch (mode) {
-        case MODE_CSR: return c ? launch_mode_workers<MODE_CSR, true>(h, a, big_workers, st) : launch_mode_workers<MODE_CSR, false>(h, a, big_workers, st);
-        case MODE_LINEAR: return c ? launch_mode_workers<MODE_LINEAR, true>(h, a, big_workers, st) : launch_mode_workers<MODE_LINEAR, false>(h, a, big_workers, st);
-        case MODE_DT: return c ? launch_mode_workers<MODE_DT, true>(h, a, big_workers, st) : launch_mode_workers<MODE_DT, false>(h, a, big_workers, st);
-        case MODE_RF: return c ? launch_mode_workers<MODE_RF, true>(h, a, big_workers, st) : launch_mode_workers<MODE_RF, false>(h, a, big_workers, st);
-        case MODE_GBT: return c ? launch_mode_workers<MODE_GBT, true>(h, a, big_workers, st) : launch_mode_workers<MODE_GBT, false>(h, a, big_workers, st);
+        case MODE_CSR: FD_DISPATCH(MODE_CSR);
+        case MODE_LINEAR: FD_DISPATCH(MODE_LINEAR);
+        case MODE_DT: FD_DISPATCH(MODE_DT);
+        case MODE_RF: FD_DISPATCH(MODE_RF);
+        case MODE_GBT: FD_DISPATCH(MODE_GBT);
     }
+#undef FD_DISPATCH
     return cudaErrorInvalidValue;
 }
 
 cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st) {
-    return launch_rows_workers(h, mode, a, BIG_WORKERS, st);
+    return launch_rows_workers(h, mode, a, MED_CTAS, BIG_WORKERS, st);
 }
 
 cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, const unsigned long long* tmp,

@@ -12,8 +12,19 @@ __host__ __device__ constexpr int row_warps(int tl) { return tl == 8 ? 16 : 8; }
 constexpr long long ROWS_FOR_SMALL_TABLES = 65536;  // batches at least this large use TL = 8
 constexpr int ROW_CH = 1024;                 // bytes per staged window
 constexpr int ROW_RAWBUF = ROW_CH + 16;      // + slack for word over-reads at the end
-constexpr int BIG_LOG2 = 16;                 // largest wide table (global memory) for dialogues that overflow it
-constexpr int BIG_WORKERS = 148;             // CTAs (one warp each) of the wide-table kernel
+// Dialogues that overflow the shared-memory table are deferred to wide tables in global memory, in two classes
+// by size (a dialogue of b bytes has at most b/2 + 1 tokens, which bounds the table it can need):
+//   medium: table <= 2^MED_LOG2 slots (32 KiB, stays in L2): 8 warps per CTA, MED_CTAS CTAs -> thousands of warps
+//   large : table <= 2^BIG_LOG2 slots: one warp per CTA, BIG_WORKERS CTAs (rare: dialogues beyond ~6 KB)
+constexpr int MED_LOG2 = 12;
+constexpr int MED_WARPS = 8;
+constexpr int MED_CTAS = 296;
+constexpr int BIG_LOG2 = 16;
+constexpr int BIG_WORKERS = 148;
+constexpr size_t wide_pool_slots(int med_ctas, int big_workers) {
+    return ((size_t)med_ctas * MED_WARPS << MED_LOG2) > ((size_t)big_workers << BIG_LOG2) ? ((size_t)med_ctas * MED_WARPS << MED_LOG2)
+                                                                                         : ((size_t)big_workers << BIG_LOG2);
+}
 
 enum Mode { MODE_CSR = 0, MODE_LINEAR = 1, MODE_DT = 2, MODE_RF = 3, MODE_GBT = 4 };
 
@@ -53,7 +64,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
                              int lane);
 
 cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st);
-cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int big_workers, cudaStream_t st);
+cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st);
 cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, const unsigned long long* tmp,
                                 long long n_rows, long long* bsum, long long* rowptr, int32_t* out_idx, double* out_val,
                                 bool scan_only, cudaStream_t st);
