@@ -190,6 +190,7 @@ k_rows(const RowArgs a) {
 
     if (BIG && (long long)blockIdx.x * ROW_WARPS >= (long long)(BIG == 1 ? a.ctrl->big_count : a.ctrl->big2_count))
         return;  // nothing deferred to this CTA
+    if (!BIG && a.pick_shape && a.ctrl->shape != TL) return;  // the other shape was picked for this call
     for (int i = threadIdx.x; i < m.sw_cap; i += blockDim.x) swt[i] = m.sw_tab[i];
     for (int i = threadIdx.x; i < m.n_sw; i += blockDim.x) sww[i] = m.sw_words[i];
     if (lane == 0) {
@@ -859,20 +860,18 @@ __global__ void k_gather_csr(const unsigned long long* __restrict__ tmp, const l
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
+// large batches: pick the kernel shape from the mean dialogue length, on the device (no host synchronisation)
+__global__ void k_pick_shape(const int64_t* __restrict__ offs, long long n_rows, Ctrl* ctrl) {
+    const long long mean = (offs[n_rows] - offs[0]) / (n_rows > 0 ? n_rows : 1);
+    ctrl->shape = mean <= MEAN_BYTES_FOR_SMALL_TABLES ? 8 : 9;
+}
+
 template <int MODE, bool CLEAN, int TL>
-static cudaError_t launch_shape(fd_handle* h, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st) {
+static cudaError_t launch_main(fd_handle* h, const RowArgs& a, cudaStream_t st) {
     constexpr int NW = row_warps(TL);
     const size_t smem = a.m.sw_smem_bytes() + (size_t)NW * sizeof(WarpSmem<TL>);
-    const size_t smem_med = a.m.sw_smem_bytes() + (size_t)MED_WARPS * sizeof(WarpSmem<TL>);
-    const size_t smem_big = a.m.sw_smem_bytes() + sizeof(WarpSmem<TL>);
     auto kern = k_rows<MODE, CLEAN, 0, TL>;
-    auto kmed = k_rows<MODE, CLEAN, 1, TL>;
-    auto kbig = k_rows<MODE, CLEAN, 2, TL>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(kmed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_med);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(kbig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_big);
     if (e != cudaSuccess) return e;
     int occ = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * NW, smem);
@@ -881,17 +880,42 @@ static cudaError_t launch_shape(fd_handle* h, const RowArgs& a, int med_ctas, in
     long long grid = std::min<long long>((long long)h->sm_count * occ, (a.n_rows + NW - 1) / NW);
     if (grid < 1) grid = 1;
     kern<<<(unsigned)grid, 32 * NW, smem, st>>>(a);
-    kmed<<<med_ctas, 32 * MED_WARPS, smem_med, st>>>(a);
-    kbig<<<big_workers, 32, smem_big, st>>>(a);
-    h->launches += 3;
+    h->launches += 1;
     return cudaGetLastError();
 }
 
-// big batches: small tables / more warps per SM; micro-batches: larger tables (fewer deferred dialogues)
 template <int MODE, bool CLEAN>
-static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st) {
-    return a.n_rows >= ROWS_FOR_SMALL_TABLES ? launch_shape<MODE, CLEAN, 8>(h, a, med_ctas, big_workers, st)
-                                             : launch_shape<MODE, CLEAN, 9>(h, a, med_ctas, big_workers, st);
+static cudaError_t launch_wide(fd_handle* h, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st) {
+    const size_t smem_med = a.m.sw_smem_bytes() + (size_t)MED_WARPS * sizeof(WarpSmem<9>);
+    const size_t smem_big = a.m.sw_smem_bytes() + sizeof(WarpSmem<9>);
+    auto kmed = k_rows<MODE, CLEAN, 1, 9>;
+    auto kbig = k_rows<MODE, CLEAN, 2, 9>;
+    cudaError_t e = cudaFuncSetAttribute(kmed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_med);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kbig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_big);
+    if (e != cudaSuccess) return e;
+    kmed<<<med_ctas, 32 * MED_WARPS, smem_med, st>>>(a);
+    kbig<<<big_workers, 32, smem_big, st>>>(a);
+    h->launches += 2;
+    return cudaGetLastError();
+}
+
+// Micro-batches always take the 512-slot shape (fewer deferrals, lower latency).  Large batches let the device
+// choose: both shapes are launched and the one that was not picked exits at once.
+template <int MODE, bool CLEAN>
+static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a0, int med_ctas, int big_workers, cudaStream_t st) {
+    RowArgs a = a0;
+    cudaError_t e;
+    if (a.n_rows >= ROWS_FOR_SMALL_TABLES) {
+        a.pick_shape = 1;
+        k_pick_shape<<<1, 1, 0, st>>>(a.offs, a.n_rows, a.ctrl);
+        h->launches += 1;
+        e = launch_main<MODE, CLEAN, 8>(h, a, st);
+        if (e != cudaSuccess) return e;
+    }
+    e = launch_main<MODE, CLEAN, 9>(h, a, st);
+    if (e != cudaSuccess) return e;
+    return launch_wide<MODE, CLEAN>(h, a, med_ctas, big_workers, st);
 }
 
 // the caller provides a.big_tabs with wide_pool_slots(med_ctas, big_workers) slots

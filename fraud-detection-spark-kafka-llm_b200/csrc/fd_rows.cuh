@@ -9,7 +9,9 @@ namespace fd {
 //   TL = 9: 512-slot count tables,  8 warps per CTA -> 24 warps per SM; for micro-batches, where fewer dialogues
 //           overflow into the wide-table kernel (which runs after the main one and would add to the latency)
 __host__ __device__ constexpr int row_warps(int tl) { return tl == 8 ? 16 : 8; }
-constexpr long long ROWS_FOR_SMALL_TABLES = 65536;  // batches at least this large use TL = 8
+constexpr long long ROWS_FOR_SMALL_TABLES = 65536;  // batches at least this large may use TL = 8 ...
+constexpr long long MEAN_BYTES_FOR_SMALL_TABLES = 1400;  // ... when their dialogues average at most this many bytes
+                                                         // (longer ones would mostly overflow a 256-slot table)
 constexpr int ROW_CH = 1024;                 // bytes per staged window
 constexpr int ROW_RAWBUF = ROW_CH + 16;      // + slack for word over-reads at the end
 // Dialogues that overflow the shared-memory table are deferred to wide tables in global memory, in two classes
@@ -47,6 +49,7 @@ struct RowArgs {
     Ctrl* ctrl;
     long long* big_rows;
     long long big_cap;
+    int pick_shape;  // 1: both main-kernel shapes are launched and ctrl->shape says which one runs
     unsigned long long* big_tabs;
     // featurize outputs (staging)
     int32_t* row_nnz;

@@ -78,6 +78,39 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    if "c1" in want and rank == 0:
+        # C1: the reference's own shape -- the SHIPPED model (HashingTF 10000 + IDF + LogisticRegression) on 1,600
+        # dialogues of about 375 tokens (the CSV itself is not distributable), plus 1M such dialogues for throughput
+        import tarfile, tempfile
+        d = tempfile.mkdtemp()
+        with tarfile.open(os.path.join(ROOT, "tests", "golden", "shipped_model.tar.gz")) as tf:
+            tf.extractall(d, filter="data")
+        model = fd.PipelineModel.load(os.path.join(d, "dialogue_classification_model"))
+        h = model.handle(local)
+        small, _ = corpus.sample(1600, tokens=375, device="cpu", seed=11)
+        hd, ho = small.data.pin_memory(), small.offs.pin_memory()
+        hp, hq, hr = (torch.empty(s_, dtype=torch.float64).pin_memory() for s_ in ((1600,), (1600, 2), (1600, 2)))
+        lat = []
+        for i in range(60):
+            t0 = time.perf_counter()
+            h.call("fd_transform_host", P(hd), P(ho), 1600, 1, P(hp), P(hq), P(hr))
+            lat.append((time.perf_counter() - t0) * 1e3)
+        lat = lat[10:]
+        big, _ = corpus.sample(1_000_000, tokens=375, device=dev, seed=12)
+        n = big.n_rows
+        out = [torch.empty(n, dtype=torch.float64, device=dev), torch.empty((n, 2), dtype=torch.float64, device=dev),
+               torch.empty((n, 2), dtype=torch.float64, device=dev)]
+        sp = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        step = lambda: h.call("fd_transform", P(big.data), P(big.offs), n, 1, P(out[0]), P(out[1]), P(out[2]), sp)
+        for _ in range(3):
+            step()
+        ms = timed(step, 5, dev)
+        print(json.dumps({"config": "C1 shipped LR model, 375-token dialogues", "batch_1600_host_path_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99))},
+                          "batch_1600_dialogues_per_s": 1600 / float(np.percentile(lat, 50)) * 1e3, "rows_1M_ms_per_pass": ms,
+                          "rows_1M_dialogues_per_s": n / ms * 1e3, "L_bar": float(big.offs[-1].item()) / n,
+                          "algorithmic_GBps": n * (float(big.offs[-1].item()) / n + 48) / ms / 1e6}))
+        del big, out, model
+
     if "c3" in want:
         n = a.c3_rows // world
         pk, _ = corpus.sample(n, tokens=200, device=dev, seed=100 + rank)
