@@ -44,6 +44,54 @@ int ensure_ws(fd_handle* h, size_t bytes) {
 }
 
 template <typename T>
+static int upload(fd_handle* h, T** dst, const T* src, size_t n);
+
+// The fused kernels never form the tf-idf value of a split feature: x = count * idf[f] is monotone in the integer
+// count (idf >= 0), so "x <= threshold" is the same as "count <= c*" with c* = the largest count whose PRODUCT, rounded
+// exactly as the device would round it, is still <= threshold.  c* is found here once per (forest, idf) pair and
+// stored in the low word of the node's threshold field.  Any negative or NaN idf entry disables the shortcut.
+int prepare_fused(fd_handle* h) {
+    if (!h->fused_dirty) return FD_OK;
+    Model& m = h->m;
+    h->fused_dirty = false;
+    m.int_walk = 0;
+    if (m.classifier != 2 || h->host_nodes.empty()) return FD_OK;
+    const bool has_idf = !h->host_idf.empty();
+    std::vector<Node> q = h->host_nodes;
+    for (auto& nd : q) {
+        if (nd.feat < 0) continue;
+        const double w = has_idf ? h->host_idf[(size_t)nd.feat] : 1.0;
+        const double thr = nd.thr;
+        if (!(w >= 0.0)) return FD_OK;  // negative or NaN weight: keep the floating-point walk
+        long long c;
+        if (!(thr >= 0.0)) c = -1;                       // also NaN: "x <= NaN" is never true
+        else if (w == 0.0) c = 0x7FFFFFFF;               // x is 0.0 whatever the count
+        else {
+            const double g = std::floor(thr / w);
+            c = g >= 2147483646.0 ? 2147483646LL : (long long)g;
+            volatile double prod;                        // one IEEE multiply, as __dmul_rn on the device
+            for (;;) {
+                prod = (double)(c + 1) * w;
+                if (c + 1 <= 2147483646LL && prod <= thr) ++c; else break;
+            }
+            for (;;) {
+                prod = (double)c * w;
+                if (c >= 0 && prod > thr) --c; else break;
+            }
+        }
+        int32_t ci = (int32_t)c;
+        uint64_t bits;
+        memcpy(&bits, &nd.thr, 8);
+        bits = (bits & 0xFFFFFFFF00000000ULL) | (uint32_t)ci;
+        memcpy(&nd.thr, &bits, 8);
+    }
+    int rc = upload(h, &m.nodes_q, q.data(), q.size());
+    if (rc) return rc;
+    m.int_walk = 1;
+    return FD_OK;
+}
+
+template <typename T>
 static int upload(fd_handle* h, T** dst, const T* src, size_t n) {
     if (*dst) {
         FD_CUDA(h, cudaFree(*dst));
@@ -91,6 +139,7 @@ int fd_destroy(fd_handle* h) {
     cudaFree(m.idf);
     cudaFree(m.coef);
     cudaFree(m.nodes);
+    cudaFree(m.nodes_q);
     cudaFree(m.roots);
     cudaFree(m.leaf2);
     cudaFree(m.leaf_prob);
@@ -224,10 +273,17 @@ int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary) {
 int fd_set_idf(fd_handle* h, const double* idf, int32_t num_features) {
     if (!h) return FD_ERR_INVALID;
     FD_CUDA(h, cudaSetDevice(h->device));
-    if (!idf) return upload(h, &h->m.idf, (const double*)nullptr, 0);
+    h->fused_dirty = true;
+    if (!idf) {
+        h->host_idf.clear();
+        int rc0 = upload(h, &h->m.idf, (const double*)nullptr, 0);
+        return rc0 ? rc0 : prepare_fused(h);
+    }
     if (num_features != h->m.num_features)
         return set_err(h, FD_ERR_INVALID, "idf size %d != numFeatures %d", num_features, h->m.num_features);
-    return upload(h, &h->m.idf, idf, (size_t)num_features);
+    h->host_idf.assign(idf, idf + num_features);
+    int rc = upload(h, &h->m.idf, idf, (size_t)num_features);
+    return rc ? rc : prepare_fused(h);  // model upload is where allocation belongs, not the compute calls
 }
 
 int fd_set_linear(fd_handle* h, const double* coef_dense, int32_t num_features, double intercept, double threshold) {
@@ -242,6 +298,7 @@ int fd_set_linear(fd_handle* h, const double* coef_dense, int32_t num_features, 
     h->m.raw_threshold = threshold <= 0.0 ? -INFINITY : (threshold >= 1.0 ? INFINITY : std::log(threshold / (1.0 - threshold)));
     h->m.classifier = 1;
     h->m.n_classes = 2;
+    h->m.int_walk = 0;
     return FD_OK;
 }
 
@@ -310,12 +367,14 @@ int fd_set_forest(fd_handle* h, int32_t kind, int32_t n_trees, const int32_t* tr
     if (!rc) rc = upload(h, &m.roots, roots.data(), roots.size());
     if (!rc && kind == FD_KIND_GBT) rc = upload(h, &m.tree_w, tree_weights, (size_t)n_trees);
     if (rc) return rc;
+    h->host_nodes = nodes;
+    h->fused_dirty = true;
     m.kind = kind;
     m.n_trees = n_trees;
     m.n_classes = 2;
     m.n_nodes = total;
     m.classifier = 2;
-    return FD_OK;
+    return prepare_fused(h);
 }
 
 }  // extern "C"

@@ -70,7 +70,7 @@ static int run_featurize_pass(fd_handle* h, const uint8_t* text, const int64_t* 
     a.offs = offs;
     a.n_rows = n_rows;
     a.flags = flags;
-    a.m = h->m;
+    a.m = h->m;  // (after prepare_fused)
     fill_slot(a, h->ws, n_rows);
     a.row_nnz = reinterpret_cast<int32_t*>(h->ws + off_nnz);
     a.row_tmpoff = reinterpret_cast<long long*>(h->ws + off_tmpoff);
@@ -183,6 +183,8 @@ int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev,
     if (n_rows == 0) return FD_OK;
     if (!out_pred_dev || !out_prob_dev || !out_raw_dev) return set_err(h, FD_ERR_INVALID, "null output column");
     FD_CUDA(h, cudaSetDevice(h->device));
+    rc = prepare_fused(h);
+    if (rc) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     rc = ensure_ws(h, slot_bytes(n_rows));
     if (rc) return rc;
@@ -192,7 +194,7 @@ int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev,
     a.offs = offs_dev;
     a.n_rows = n_rows;
     a.flags = flags;
-    a.m = h->m;
+    a.m = h->m;  // (after prepare_fused)
     fill_slot(a, h->ws, n_rows);
     a.pred = out_pred_dev;
     a.prob = out_prob_dev;
@@ -228,6 +230,8 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
     if (rc) return rc;
     if (n_rows == 0) return FD_OK;
     FD_CUDA(h, cudaSetDevice(h->device));
+    rc = prepare_fused(h);
+    if (rc) return rc;
     for (int i = 0; i < 3; ++i)
         if (!h->hs[i]) FD_CUDA(h, cudaStreamCreateWithFlags(&h->hs[i], cudaStreamNonBlocking));
     if (!h->pinned_ctrl) FD_CUDA(h, cudaMallocHost((void**)&h->pinned_ctrl, 4 * sizeof(Ctrl)));
@@ -277,7 +281,7 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
         a.offs = reinterpret_cast<const int64_t*>(base + off_offs);
         a.n_rows = nr;
         a.flags = flags;
-        a.m = h->m;
+        a.m = h->m;  // (after prepare_fused)
         a.pred = reinterpret_cast<double*>(base + off_pred);
         a.prob = reinterpret_cast<double*>(base + off_prob);
         a.raw = reinterpret_cast<double*>(base + off_raw);

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/fdb200.h"
 
@@ -60,6 +61,8 @@ struct Model {
     double intercept = 0.0, raw_threshold = 0.0;
     int kind = 0, n_trees = 0, n_classes = 2;
     Node* nodes = nullptr;
+    Node* nodes_q = nullptr;   // same forest with every split threshold pre-quantised to a TERM COUNT (see prepare_fused)
+    int int_walk = 0;          // 1: the fused kernels walk nodes_q with integer compares
     int32_t* roots = nullptr;  // absolute root index per tree
     double2* leaf2 = nullptr;  // DT: raw class stats, RF: stats / total (0,0 when total == 0)
     double2* leaf_prob = nullptr;  // DT: stats / total, divided once on the host (IEEE division: same bits as on the device)
@@ -89,6 +92,10 @@ struct fd_handle {
     char* hbuf[3] = {nullptr, nullptr, nullptr};
     size_t hbuf_bytes[3] = {0, 0, 0};
     fd::Ctrl* pinned_ctrl = nullptr;
+    // host copies needed to (re)build nodes_q when the idf vector or the forest changes
+    std::vector<fd::Node> host_nodes;
+    std::vector<double> host_idf;
+    bool fused_dirty = false;
 };
 
 namespace fd {
@@ -96,6 +103,7 @@ namespace fd {
 int set_err(fd_handle* h, int code, const char* fmt, ...);
 int cuda_fail(fd_handle* h, cudaError_t e, const char* what);
 int ensure_ws(fd_handle* h, size_t bytes);
+int prepare_fused(fd_handle* h);
 
 #define FD_CUDA(h, call)                                             \
     do {                                                             \

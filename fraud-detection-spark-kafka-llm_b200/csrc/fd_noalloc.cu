@@ -76,6 +76,8 @@ extern "C" int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const
     else if (h->m.classifier == 2) mode = h->m.kind == FD_KIND_DT ? MODE_DT : (h->m.kind == FD_KIND_RF ? MODE_RF : MODE_GBT);
     else return set_err(h, FD_ERR_STATE, "no classifier stage set (fd_set_linear / fd_set_forest)");
     FD_CUDA(h, cudaSetDevice(h->device));
+    if (h->fused_dirty)  // cannot happen: fd_set_idf / fd_set_forest prepare the model (and allocate) at upload time
+        return set_err(h, FD_ERR_STATE, "model not prepared");
     char* base = nullptr;
     int rc = scratch_address(h, &base);
     if (rc) return rc;
@@ -86,7 +88,7 @@ extern "C" int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const
     a.offs = offs_dev;
     a.n_rows = n_rows;
     a.flags = flags;
-    a.m = h->m;
+    a.m = h->m;  // (after prepare_fused)
     a.ctrl = reinterpret_cast<Ctrl*>(base);
     a.big_tabs = reinterpret_cast<unsigned long long*>(base + NA_CTRL);
     a.big_rows = reinterpret_cast<long long*>(base + NA_CTRL + NA_TABS);

@@ -673,6 +673,21 @@ __device__ __forceinline__ void write_result(const RowArgs& a, long long row, in
 // walk one tree with the dialogue's (bucket -> count) table; returns the absolute leaf index
 __device__ __forceinline__ int walk_tree(const Model& m, const unsigned long long* tab, int log2cap, int root, Node& leaf) {
     int n = root;
+    if (m.int_walk) {
+        // thresholds pre-quantised to term counts (prepare_fused): a level is one node load, one table probe, one
+        // integer compare -- no idf load and no fp64 on the dependent chain
+        for (;;) {
+            const uint4 q = __ldg(reinterpret_cast<const uint4*>(m.nodes_q + n));
+            if ((int)q.z < 0) {
+                leaf.thr = __hiloint2double((int)q.y, (int)q.x);
+                leaf.feat = (int)q.z;
+                leaf.child = (int)q.w;
+                return n;
+            }
+            const int cnt = (int)tab_lookup(tab, log2cap, q.z);
+            n = (int)q.w + ((cnt <= (int)q.x) ? 0 : 1);
+        }
+    }
     for (;;) {
         const uint4 q = __ldg(reinterpret_cast<const uint4*>(m.nodes + n));
         Node nd;
