@@ -100,3 +100,69 @@ def test_pipeline_fit_end_to_end(fd, tmp_path):
     assert torch.equal(again.transform(test)["prediction"], out["prediction"])
     imp = model.stages[-1].featureImportances
     assert abs(imp.sum() - 1.0) < 1e-9 and (imp > 0).sum() >= 5
+
+
+def test_training_edge_cases(fd):
+    """Degenerate inputs the level loop must survive: a pure node at the root, rows without any feature, fewer rows
+    than a warp, maxDepth = 0, and a feature whose every value is identical (no threshold)."""
+    h = fd.Handle(0)
+    mk = lambda depth, trees=1: training.ForestTrainer(training.CudaTreeBackend(h), 8, n_trees=trees, max_depth=depth, feature_subset_strategy="all", seed=3)
+    # all labels equal -> the root stays a leaf holding every row
+    rows_idx = [[0, 1], [1], [], [2, 3]] * 3
+    rows_val = [[1.0, 2.0], [1.0], [], [3.0, 1.0]] * 3
+    rp, ix, vl = (x.cuda() for x in _csr(rows_idx, rows_val))
+    t = mk(4).fit(rp, ix, vl, torch.zeros(12, dtype=torch.uint8).cuda())[0]
+    assert t.n_nodes == 1 and t.stats[0].tolist() == [12.0, 0.0] and t.prediction[0] == 0.0
+    # labels decided by the PRESENCE of feature 2 (rows without it are all-absent on that column)
+    y = np.array([0, 0, 0, 1] * 3, dtype=np.uint8)
+    t = mk(3).fit(rp, ix, vl, torch.from_numpy(y).cuda())[0]
+    assert t.feature[0] in (2, 3) and t.n_nodes == 3 and sorted(t.stats[1:].sum(axis=1).tolist()) == [3.0, 9.0]
+    assert {tuple(r) for r in t.stats[1:].tolist()} == {(9.0, 0.0), (0.0, 3.0)}
+    # maxDepth = 0: a single leaf with the class totals
+    t = mk(0).fit(rp, ix, vl, torch.from_numpy(y).cuda())[0]
+    assert t.n_nodes == 1 and t.stats[0].tolist() == [9.0, 3.0]
+    # constant feature (same value in every row) yields no threshold and is never chosen
+    rows_idx = [[5]] * 10
+    rows_val = [[2.5]] * 10
+    rp, ix, vl = (x.cuda() for x in _csr(rows_idx, rows_val))
+    y = np.array([0, 1] * 5, dtype=np.uint8)
+    t = mk(3).fit(rp, ix, vl, torch.from_numpy(y).cuda())[0]
+    assert t.n_nodes == 1 and t.stats[0].tolist() == [5.0, 5.0]
+    # an empty shard (this rank holds no rows) must not break the kernels
+    rp0 = torch.zeros(1, dtype=torch.int64).cuda()
+    t = mk(2).fit(rp0, torch.zeros(0, dtype=torch.int32).cuda(), torch.zeros(0, dtype=torch.float64).cuda(), torch.zeros(0, dtype=torch.uint8).cuda())[0]
+    assert t.n_nodes == 1 and t.stats[0].tolist() == [0.0, 0.0]
+
+
+def test_decision_tree_pipeline_matches_oracle_end_to_end(fd):
+    """Pipeline.fit with a DecisionTreeClassifier on text: featurise on the GPU, train on the GPU, and compare the
+    tree with the oracle trained on the oracle's own features (thresholds from the same full-sample rule)."""
+    from helpers import oracle_for
+    from oracle import spark_oracle as so
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    corpus = synth.SynthCorpus(n_words=400, seed=8)
+    planted = {"ids": list(range(corpus.n_stop + 30, corpus.n_stop + 36)), "rate": 0.15}
+    pk, lab = corpus.sample(900, tokens=40, device="cpu", seed=4, planted=planted)
+    data, offs = pk.data.numpy(), pk.offs.numpy()
+    texts = [bytes(data[offs[i]:offs[i + 1]]).decode() for i in range(900)]
+    nf = 512
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"), fd.StopWordsRemover(inputCol="words", outputCol="filtered_words"),
+              fd.HashingTF(inputCol="filtered_words", outputCol="raw_features", numFeatures=nf),
+              fd.IDF(inputCol="raw_features", outputCol="features"),
+              fd.DecisionTreeClassifier(featuresCol="features", labelCol="labels", maxDepth=5)]
+    model = fd.Pipeline(stages=stages).fit(texts, labels=lab.numpy())
+    tree = model.stages[-1].trees[0]
+    # oracle side: features from the oracle featuriser with the fitted idf, then oracle training
+    feat_only = fd.PipelineModel(model.stages[:4])
+    ora = oracle_for(feat_only)
+    rows = [ora.featurize(t.encode())[:2] for t in texts]
+    rows_idx, rows_val = [r[0] for r in rows], [r[1] for r in rows]
+    fi = np.asarray([x for r in rows_idx for x in r]); fv = np.asarray([x for r in rows_val for x in r])
+    thresholds = training.find_splits(fi, fv, nf, 900.0, 31)
+    exp = _oracle_forest(rows_idx, rows_val, lab.numpy().astype(np.uint8), nf, thresholds, np.ones((1, 900), np.uint8), lambda t, n: np.arange(nf), 5)
+    _same_tree(tree, exp[0])
+    assert tree.n_nodes >= 7
+    # and the fitted idf equals the oracle's IDF.fit on the same rows
+    tf_rows = [so.featurize_bytes(t.encode(), ora.stop_words, nf, None)[:2] for t in texts]
+    idf, df, m = so.idf_fit(tf_rows, nf)
+    assert np.array_equal(idf.view(np.uint64), model.stages[3].idf.view(np.uint64)) and m == 900
