@@ -9,7 +9,7 @@ from .evaluation import BinaryClassificationEvaluator, MulticlassClassificationE
 from .packing import PackedText, pack_strings
 from .pipeline import Pipeline, PipelineModel, Row, TransformResult, predict_and_get_label
 from .serving import MicroBatcher, classify_batch
-from .stages import (DecisionTreeClassificationModel, DecisionTreeClassifier, RandomForestClassifier, GBTClassificationModel, HashingTF, IDF, IDFModel,
+from .stages import (CountVectorizer, CountVectorizerModel, DecisionTreeClassificationModel, DecisionTreeClassifier, RandomForestClassifier, GBTClassificationModel, HashingTF, IDF, IDFModel,
                      LogisticRegressionModel, RandomForestClassificationModel, StopWordsRemover, Tokenizer,
                      load_default_stop_words, load_stage)
 

@@ -24,6 +24,7 @@ SIGNATURES = {
     "fd_version": (C.c_int, []),
     "fd_set_stopwords": (C.c_int, [_p, _p, _p, _i32, _i32]),
     "fd_set_hashing": (C.c_int, [_p, _i32, _i32]),
+    "fd_set_vocabulary": (C.c_int, [_p, _p, _p, _i32, _i32]),
     "fd_hash_terms": (C.c_int, [_p, _p, _i32, _i32, _p]),
     "fd_set_idf": (C.c_int, [_p, _p, _i32]),
     "fd_set_linear": (C.c_int, [_p, _p, _i32, _f64, _f64]),

@@ -136,6 +136,9 @@ int fd_destroy(fd_handle* h) {
     cudaFree(m.sw_tab);
     cudaFree(m.sw_words);
     cudaFree(m.sw_pool);
+    cudaFree(m.vocab_tab);
+    cudaFree(m.vocab_words);
+    cudaFree(m.vocab_pool);
     cudaFree(m.idf);
     cudaFree(m.coef);
     cudaFree(m.nodes);
@@ -164,6 +167,7 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
     FD_CUDA(h, cudaSetDevice(h->device));
     Model& m = h->m;
     m.empty_is_stop = 0;
+    m.drop_empty = m.empty_absent;
     if (n_words == 0) {
         if (m.sw_tab) cudaFree(m.sw_tab);
         if (m.sw_words) cudaFree(m.sw_words);
@@ -191,6 +195,7 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
                 if (c >= 'A' && c <= 'Z') c |= 0x20;
         if (len == 0) {
             m.empty_is_stop = 1;
+            m.drop_empty = 1;
             continue;
         }
         bool dup = false;
@@ -267,6 +272,80 @@ int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary) {
     m.mod_magic = m.mod_pow2 ? 0u : (uint32_t)((1ULL << 32) / (uint64_t)num_features);
     m.mod_r32 = (uint32_t)((1ULL << 32) % (uint64_t)num_features);
     m.empty_idx = nonneg_mod_host(murmur3_host(nullptr, 0), num_features);
+    if (m.vocab_tab) cudaFree(m.vocab_tab);
+    if (m.vocab_words) cudaFree(m.vocab_words);
+    if (m.vocab_pool) cudaFree(m.vocab_pool);
+    m.vocab_tab = nullptr;
+    m.vocab_words = nullptr;
+    m.vocab_pool = nullptr;
+    m.vocab_cap = 0;
+    m.empty_absent = 0;
+    m.drop_empty = m.empty_is_stop;
+    return FD_OK;
+}
+
+int fd_set_vocabulary(fd_handle* h, const uint8_t* words, const int32_t* offs, int32_t n_words, int32_t binary) {
+    if (!h || n_words <= 0 || !words || !offs) return set_err(h, FD_ERR_INVALID, "bad vocabulary arguments");
+    FD_CUDA(h, cudaSetDevice(h->device));
+    Model& m = h->m;
+    std::vector<uint4> recs((size_t)n_words);
+    std::vector<uint32_t> h1((size_t)n_words), h2((size_t)n_words);
+    std::vector<uint8_t> pool;
+    int empty_id = -1;
+    for (int i = 0; i < n_words; ++i) {
+        const int len = offs[i + 1] - offs[i];
+        if (len < 0) return set_err(h, FD_ERR_INVALID, "vocabulary offsets not ascending");
+        const uint8_t* w = words + offs[i];
+        uint32_t b[3] = {0, 0, 0};
+        for (int k = 0; k < len && k < 12; ++k) b[k >> 2] |= (uint32_t)w[k] << (8 * (k & 3));
+        if (len <= 12) {
+            recs[i] = make_uint4((uint32_t)len, b[0], b[1], b[2]);
+        } else {
+            recs[i] = make_uint4((uint32_t)len | 0x80000000u, (uint32_t)pool.size(), 0, 0);
+            pool.insert(pool.end(), w, w + len);
+        }
+        h1[i] = murmur3_host(w, len);
+        h2[i] = sw_key((uint32_t)len, b[0], b[1], b[2]);
+        if (len == 0) empty_id = i;
+    }
+    int cap = 64;
+    while (cap < 4 * n_words) cap <<= 1;
+    std::vector<uint2> tab;
+    for (int attempt = 0;; ++attempt, cap <<= 1) {
+        if (attempt > 3) return set_err(h, FD_ERR_INVALID, "could not index the vocabulary (duplicate terms?)");
+        tab.assign((size_t)cap, make_uint2(0u, 0u));
+        const uint32_t mask = (uint32_t)cap - 1u;
+        bool ok = true;
+        for (int i = 0; i < n_words && ok; ++i) {
+            uint32_t id = (uint32_t)i;
+            uint32_t slot = h1[id] & mask;
+            ok = false;
+            for (int kick = 0; kick < 1024; ++kick) {
+                if (tab[slot].y == 0u) {
+                    tab[slot] = make_uint2(h1[id], id + 1u);
+                    ok = true;
+                    break;
+                }
+                const uint32_t other = tab[slot].y - 1u;
+                tab[slot] = make_uint2(h1[id], id + 1u);
+                id = other;
+                const uint32_t s1 = h1[id] & mask, s2 = h2[id] & mask;
+                slot = (slot == s1) ? s2 : s1;
+            }
+        }
+        if (ok) break;
+    }
+    int rc = upload(h, &m.vocab_tab, tab.data(), tab.size());
+    if (!rc) rc = upload(h, &m.vocab_words, recs.data(), recs.size());
+    if (!rc) rc = upload(h, &m.vocab_pool, pool.data(), pool.size());
+    if (rc) return rc;
+    m.vocab_cap = cap;
+    m.num_features = n_words;
+    m.binary = binary ? 1 : 0;
+    m.mod_pow2 = 0;
+    m.empty_absent = empty_id < 0;
+    m.empty_idx = empty_id < 0 ? 0u : (uint32_t)empty_id;
+    m.drop_empty = m.empty_is_stop || m.empty_absent;
     return FD_OK;
 }
 

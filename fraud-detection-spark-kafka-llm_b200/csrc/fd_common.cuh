@@ -46,6 +46,14 @@ struct Model {
     int n_sw = 0;
     uint8_t* sw_pool = nullptr; // bytes of words longer than 12
     int empty_is_stop = 0;
+    int empty_absent = 0;       // vocabulary mode: the empty token is not in the vocabulary
+    int drop_empty = 0;         // empty_is_stop || empty_absent: empty tokens are not counted
+    // CountVectorizerModel vocabulary (replaces the hashing trick when vocab_cap > 0): 2-choice cuckoo table in global
+    // memory, slot = {murmur3 of the word, word id + 1}; a word sits at slot (h & mask) or (sw_key(...) & mask)
+    uint2* vocab_tab = nullptr;
+    int vocab_cap = 0;
+    uint4* vocab_words = nullptr;  // per word: x = len (|0x80000000 when > 12 bytes), y/z/w = first 12 bytes or y = pool offset
+    uint8_t* vocab_pool = nullptr;
     // hashing
     int32_t num_features = 0;
     int binary = 0;
@@ -144,6 +152,12 @@ inline uint32_t murmur3_host(const uint8_t* p, int n, uint32_t seed = 42u) {
     for (int i = 0; i < (n & 3); ++i) k |= (uint32_t)p[4 * nb + i] << (8 * i);
     if (n & 3) h ^= mm_k(k);
     return mm_fmix(h, (uint32_t)n);
+}
+// second hash of a term for the vocabulary's cuckoo table: a cheap mix of its length and first 12 bytes (zero padded);
+// host and device must agree
+__host__ __device__ __forceinline__ uint32_t sw_key(uint32_t n, uint32_t b0, uint32_t b1, uint32_t b2) {
+    uint32_t k = (b0 * 0x9E3779B1u) ^ (b1 * 0x85EBCA6Bu) ^ (b2 * 0xC2B2AE35u) ^ (n * 0x27D4EB2Fu);
+    return k ^ (k >> 15);
 }
 // Utils.nonNegativeMod on the signed value of h
 inline uint32_t nonneg_mod_host(uint32_t h, int32_t nf) {

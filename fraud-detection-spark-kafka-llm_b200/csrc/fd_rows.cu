@@ -73,6 +73,40 @@ __device__ __forceinline__ uint32_t feature_index(uint32_t h, const Model& m) {
     return r;
 }
 
+constexpr uint32_t NOT_IN_VOCAB = 0xFFFFFFFFu;
+
+// token bytes [s, e) filtered by the letter mask == word (same length already checked)
+__device__ __noinline__ bool long_word_equal(const uint8_t* word, const uint8_t* rb, const uint32_t* lmask, int s, int e) {
+    uint32_t i = 0;
+    for (int p = s; p < e; ++p)
+        if (((lmask[p >> 5] >> (p & 31)) & 1u) && rb[p] != word[i++]) return false;
+    return true;
+}
+
+// CountVectorizerModel: term -> vocabulary index (NOT_IN_VOCAB when absent).  h = murmur3(term), n = its length,
+// b0..b2 = its first 12 bytes; [s, e) locates it in the window for the byte compare of longer words (s < 0: a
+// multi-window token, never matched against words longer than 12 bytes -- documented limitation).
+__device__ uint32_t vocab_index(const Model& m, uint32_t h, uint32_t n, uint32_t b0, uint32_t b1, uint32_t b2, const uint8_t* rb,
+                                const uint32_t* lmask, int s, int e) {
+    const uint32_t mask = (uint32_t)m.vocab_cap - 1u;
+    const uint32_t slots[2] = {h & mask, sw_key(n, b0, b1, b2) & mask};
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const uint2 ent = __ldg(m.vocab_tab + slots[i]);
+        if (ent.y != 0u && ent.x == h) {
+            const uint4 w = __ldg(m.vocab_words + (ent.y - 1u));
+            if ((w.x & 0x7FFFFFFFu) == n) {
+                if (!(w.x & 0x80000000u)) {
+                    if (w.y == b0 && w.z == b1 && w.w == b2) return ent.y - 1u;
+                } else if (s >= 0 && long_word_equal(m.vocab_pool + w.y, rb, lmask, s, e)) {
+                    return ent.y - 1u;
+                }
+            }
+        }
+    }
+    return NOT_IN_VOCAB;
+}
+
 __device__ __forceinline__ uint32_t tab_slot(uint32_t idx, int log2cap) { return (idx * 0x9E3779B1u) >> (32 - log2cap); }
 
 // (bucket -> count) insert; returns true when the bucket is new for this dialogue
@@ -396,7 +430,7 @@ k_rows(const RowArgs a) {
         row_sp += (uint32_t)win_sp;
         if (last_letter >= 0) {
             // a letter exists in this window: empties carried from earlier windows were interior
-            if (pend && !big && !m.empty_is_stop) {
+            if (pend && !big && !m.drop_empty) {
                 bool isnew = false;
                 if (lane == 0) isnew = tab_insert(tab, TLOG2, m.empty_idx, pend, binary);
                 D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
@@ -418,7 +452,8 @@ k_rows(const RowArgs a) {
                         if (gt.n == 0) {
                             was_empty = true;
                         } else if (!(m.sw_cap && is_stop_word(swt, sww, m.sw_cap, h, gt.n, gt.b0, gt.b1, gt.b2))) {
-                            isnew = tab_insert(tab, TLOG2, feature_index(h, m), 1u, binary);
+                            const uint32_t fi = m.vocab_cap ? vocab_index(m, h, gt.n, gt.b0, gt.b1, gt.b2, rb, S.lmask, -1, -1) : feature_index(h, m);
+                            if (fi != NOT_IN_VOCAB) isnew = tab_insert(tab, TLOG2, fi, 1u, binary);
                         }
                         gt.reset();
                     }
@@ -428,7 +463,7 @@ k_rows(const RowArgs a) {
                         // empty multi-window token: interior iff a letter follows in this window
                         if (S.tok[0] <= last_letter) {
                             bool nw2 = false;
-                            if (lane == 0 && !m.empty_is_stop) nw2 = tab_insert(tab, TLOG2, m.empty_idx, 1u, binary);
+                            if (lane == 0 && !m.drop_empty) nw2 = tab_insert(tab, TLOG2, m.empty_idx, 1u, binary);
                             D += __popc(__ballot_sync(0xFFFFFFFFu, nw2));
                         } else {
                             pend += 1;
@@ -550,9 +585,14 @@ k_rows(const RowArgs a) {
 #pragma unroll
                 for (int u = 0; u < TPL; ++u) {
                     const bool interior_empty = empty[u] && s[u] <= last_letter;
-                    const bool ins = valid[u] && (empty[u] ? (interior_empty && !m.empty_is_stop) : !stop[u]);
+                    bool ins = valid[u] && (empty[u] ? (interior_empty && !m.drop_empty) : !stop[u]);
+                    uint32_t fi = m.empty_idx;
+                    if (ins && !empty[u]) {
+                        fi = m.vocab_cap ? vocab_index(m, h[u], n[u], b0[u], b1[u], b2[u], rb, S.lmask, s[u], e[u]) : feature_index(h[u], m);
+                        ins = fi != NOT_IN_VOCAB;
+                    }
                     bool isnew = false;
-                    if (ins) isnew = tab_insert(tab, TLOG2, empty[u] ? m.empty_idx : feature_index(h[u], m), 1u, binary);
+                    if (ins) isnew = tab_insert(tab, TLOG2, fi, 1u, binary);
                     D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
                     pend += __popc(__ballot_sync(0xFFFFFFFFu, empty[u] && !interior_empty));
                 }
@@ -563,7 +603,7 @@ k_rows(const RowArgs a) {
 
         // ================= end of dialogue =================
         if (last) {
-            if (!big && row_sp == 0 && !row_letter && !m.empty_is_stop) {
+            if (!big && row_sp == 0 && !row_letter && !m.drop_empty) {
                 // no separator anywhere and nothing kept: Java's split returns [""] -- one empty token
                 bool isnew = false;
                 if (lane == 0) isnew = tab_insert(tab, TLOG2, m.empty_idx, 1u, binary);

@@ -129,11 +129,11 @@ class _Plan:
                     raise ValueError("StopWordsRemover must follow the Tokenizer")
                 self._wire(st, col)
                 self.stop = st
-            elif isinstance(st, S.HashingTF):
+            elif isinstance(st, (S.HashingTF, S.CountVectorizerModel)):
                 if not self.tokenizer or self.hashing:
-                    raise ValueError("HashingTF must follow the Tokenizer")
+                    raise ValueError(f"{type(st).__name__} must follow the Tokenizer")
                 self._wire(st, col)
-                self.hashing = st
+                self.hashing = st  # the term -> index stage: hashing trick or vocabulary lookup
             elif isinstance(st, S.IDFModel):
                 if not self.hashing or self.idf:
                     raise ValueError("IDFModel must follow HashingTF")
@@ -150,13 +150,19 @@ class _Plan:
                 raise ValueError(f"stage {type(st).__name__} is not supported on the B200 path")
             col = st.getOrDefault("outputCol")
         if not self.hashing:
-            raise ValueError("pipeline needs Tokenizer -> [StopWordsRemover] -> HashingTF")
+            raise ValueError("pipeline needs Tokenizer -> [StopWordsRemover] -> HashingTF | CountVectorizerModel")
         self.features_col = col
-        nf = int(self.hashing.getOrDefault("numFeatures"))
+        nf = self.num_features
         if self.idf is not None and self.idf.idf.size != nf:
             raise ValueError("IDF vector size differs from HashingTF.numFeatures")
         if self.classifier is not None and self.classifier.numFeatures not in (0, nf):
             raise ValueError("classifier numFeatures differs from HashingTF.numFeatures")
+
+    @property
+    def num_features(self) -> int:
+        if isinstance(self.hashing, S.CountVectorizerModel):
+            return len(self.hashing.vocabulary)
+        return int(self.hashing.getOrDefault("numFeatures"))
 
     @staticmethod
     def _wire(st, col):
@@ -229,8 +235,17 @@ class PipelineModel:
             np.cumsum([len(e) for e in enc], out=offs[1:])
             blob = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
             h.call("fd_set_stopwords", _lib.ptr(blob), _lib.ptr(offs), len(enc), int(cs))
-        nf = int(p.hashing.getOrDefault("numFeatures"))
-        h.call("fd_set_hashing", nf, int(bool(p.hashing.getOrDefault("binary"))))
+        nf = p.num_features
+        if isinstance(p.hashing, S.CountVectorizerModel):
+            if float(p.hashing.getOrDefault("minTF")) != 1.0:
+                raise ValueError("CountVectorizerModel: only minTF = 1.0 is implemented on the device path")
+            enc = [w.encode("utf-8") for w in p.hashing.vocabulary]
+            offs = np.zeros(len(enc) + 1, dtype=np.int32)
+            np.cumsum([len(e) for e in enc], out=offs[1:])
+            blob = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
+            h.call("fd_set_vocabulary", _lib.ptr(blob), _lib.ptr(offs), len(enc), int(bool(p.hashing.getOrDefault("binary"))))
+        else:
+            h.call("fd_set_hashing", nf, int(bool(p.hashing.getOrDefault("binary"))))
         if p.idf is not None:
             h.call("fd_set_idf", _lib.ptr(p.idf.idf), nf)
         c = p.classifier
@@ -368,7 +383,7 @@ class Pipeline:
         tf_model = PipelineModel(feats)
         rowptr, idx, val = tf_model.featurize(batch, cleaned=cleaned, device=device)
         dev = rowptr.device
-        nf = int(tf_model._plan.hashing.getOrDefault("numFeatures"))
+        nf = tf_model._plan.num_features
         fitted: List[S.Stage] = list(feats)
         if idf:
             st = idf[0]

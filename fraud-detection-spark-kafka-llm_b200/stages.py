@@ -124,6 +124,50 @@ class HashingTF(Stage):
         self.defaultParamMap = {"outputCol": self.uid + "__output", "numFeatures": 262144, "binary": False}
 
 
+class CountVectorizerModel(Stage):
+    """``org.apache.spark.ml.feature.CountVectorizerModel`` -- the featuriser the reference's training script builds
+    (``CountVectorizer(..., vocabSize=20000)``, fraud_detection_spark.py:52).  Data: ``vocabulary: array<string>``;
+    term -> index by dictionary, terms outside the vocabulary are ignored.  Only the default ``minTF = 1.0`` is
+    implemented on the device path."""
+    spark_class = "org.apache.spark.ml.feature.CountVectorizerModel"
+    uid_prefix = "CountVectorizer"
+
+    def __init__(self, vocabulary: Sequence[str], inputCol=None, outputCol=None, binary=None, minTF=None, uid=None):
+        super().__init__(uid, inputCol=inputCol, outputCol=outputCol, binary=binary, minTF=minTF)
+        self.defaultParamMap = {"outputCol": self.uid + "__output", "vocabSize": 262144, "minDF": 1.0,
+                                "maxDF": 9.223372036854776e18, "minTF": 1.0, "binary": False}
+        self.vocabulary = list(vocabulary)
+
+    @classmethod
+    def _load(cls, path, meta):
+        obj = cls._from_metadata(meta)
+        t = sf.read_parquet_dir(os.path.join(path, "data"))
+        obj.vocabulary = list(t.column("vocabulary")[0].as_py())
+        return obj
+
+    def _write_data(self, path):
+        schema = pa.schema([pa.field("vocabulary", pa.list_(pa.field("element", pa.string(), nullable=True)))])
+        sf.write_parquet_dir(os.path.join(path, "data"), pa.Table.from_pylist([{"vocabulary": self.vocabulary}], schema=schema))
+
+
+class CountVectorizer(Stage):
+    """``org.apache.spark.ml.feature.CountVectorizer`` estimator (fraud_detection_spark.py:52); fitted on the device
+    by ``Pipeline.fit`` (term counts -> top ``vocabSize`` terms)."""
+    spark_class = "org.apache.spark.ml.feature.CountVectorizer"
+    uid_prefix = "CountVectorizer"
+
+    def __init__(self, inputCol=None, outputCol=None, vocabSize=None, minDF=None, maxDF=None, minTF=None, binary=None, uid=None):
+        super().__init__(uid, inputCol=inputCol, outputCol=outputCol, vocabSize=vocabSize, minDF=minDF, maxDF=maxDF, minTF=minTF, binary=binary)
+        self.defaultParamMap = {"outputCol": self.uid + "__output", "vocabSize": 262144, "minDF": 1.0,
+                                "maxDF": 9.223372036854776e18, "minTF": 1.0, "binary": False}
+
+    def model_from_vocabulary(self, vocabulary: Sequence[str]) -> CountVectorizerModel:
+        m = CountVectorizerModel(vocabulary, uid=self.uid)
+        m.paramMap = dict(self.paramMap)
+        m.defaultParamMap = dict(self.defaultParamMap)
+        return m
+
+
 class IDF(Stage):
     """``org.apache.spark.ml.feature.IDF`` estimator (reference fraud_detection_spark.py:53)."""
     spark_class = "org.apache.spark.ml.feature.IDF"
@@ -420,7 +464,7 @@ class RandomForestClassifier(_TreeEstimator):
         return RandomForestClassificationModel(trees, n_features, 2, uid=self.uid)
 
 
-STAGE_CLASSES = {c.spark_class: c for c in (Tokenizer, StopWordsRemover, HashingTF, IDF, IDFModel, LogisticRegressionModel,
+STAGE_CLASSES = {c.spark_class: c for c in (Tokenizer, StopWordsRemover, HashingTF, CountVectorizerModel, IDF, IDFModel, LogisticRegressionModel,
                                              DecisionTreeClassificationModel, RandomForestClassificationModel,
                                              GBTClassificationModel)}
 

@@ -69,6 +69,11 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
                      int32_t case_sensitive);
 /* HashingTF params (stages/2_HashingTF_e7eba1072633/metadata/part-00000:1): numFeatures, binary. */
 int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary);
+/* CountVectorizerModel (fraud_detection_spark.py:52; data = `vocabulary: array<string>`): use a term dictionary instead
+ * of the hashing trick.  words = the vocabulary's UTF-8 bytes back to back in index order, offs int32[n_words+1].
+ * Terms outside the vocabulary are ignored, numFeatures becomes n_words; only minTF = 1.0 semantics are implemented.
+ * A later fd_set_hashing switches back to HashingTF. */
+int fd_set_vocabulary(fd_handle* h, const uint8_t* words, const int32_t* offs, int32_t n_words, int32_t binary);
 /* HashingTF.indexOf(term) for n terms on the HOST (no device work): out[i] = nonNegativeMod(
  * murmur3_x86_32(term_i bytes, seed 42), num_features).  terms = bytes back to back, offs int32[n+1]. */
 int fd_hash_terms(const uint8_t* terms, const int32_t* offs, int32_t n, int32_t num_features, int32_t* out);

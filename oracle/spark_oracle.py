@@ -223,6 +223,42 @@ def hashing_tf(tokens: Sequence[bytes], num_features: int, binary: bool = False)
 
 
 # ---------------------------------------------------------------------------------------------
+# CountVectorizer / CountVectorizerModel        reference: fraud_detection_spark.py:52      -- parity unpinned
+# ---------------------------------------------------------------------------------------------
+def count_vectorize(tokens: Sequence[bytes], vocab_index: dict, binary: bool = False, min_tf: float = 1.0):
+    """``CountVectorizerModel.transform`` on one document: dictionary lookup, unknown terms ignored, counts filtered
+    by minTF (absolute when >= 1, else a fraction of the document's token count), indices ascending."""
+    counts = {}
+    for t in tokens:
+        i = vocab_index.get(t)
+        if i is not None:
+            counts[i] = counts.get(i, 0.0) + 1.0
+    eff = min_tf if min_tf >= 1.0 else len(tokens) * min_tf
+    idx = sorted(i for i, c in counts.items() if c >= eff)
+    return idx, [1.0 if binary else counts[i] for i in idx]
+
+
+def count_vectorizer_fit(docs: Sequence[Sequence[bytes]], vocab_size: int, min_df: float = 1.0, max_df: float = 2.0 ** 63):
+    """``CountVectorizer.fit``: total term counts and document frequencies, optional df filter, then the
+    ``vocab_size`` most frequent terms.  Spark breaks count ties by partition order (unspecified); here ties go to the
+    smaller term bytes, and so does the product code."""
+    tc, df = {}, {}
+    for d in docs:
+        seen = set()
+        for t in d:
+            tc[t] = tc.get(t, 0) + 1
+            if t not in seen:
+                seen.add(t)
+                df[t] = df.get(t, 0) + 1
+    n = len(docs)
+    lo = min_df if min_df >= 1.0 else min_df * n
+    hi = max_df if max_df >= 1.0 else max_df * n
+    terms = [t for t in tc if lo <= df[t] <= hi]
+    terms.sort(key=lambda t: (-tc[t], t))
+    return terms[:vocab_size], tc, df
+
+
+# ---------------------------------------------------------------------------------------------
 # A.5  IDF / IDFModel                  reference: fraud_detection_spark.py:53,
 #                                      stages/3_IDF_58bd96296a82/{metadata,data}
 # ---------------------------------------------------------------------------------------------
@@ -255,7 +291,7 @@ def idf_transform(idx: Sequence[int], val: Sequence[float], idf: np.ndarray) -> 
 # featurise one dialogue end to end (a1..a5)
 # ---------------------------------------------------------------------------------------------
 def featurize_bytes(raw: bytes, stop_words: Sequence[bytes], num_features: int, idf: Optional[np.ndarray],
-                    do_clean: bool = True, binary: bool = False):
+                    do_clean: bool = True, binary: bool = False, vocab_index: Optional[dict] = None):
     """raw UTF-8 bytes -> (idx ascending, tf-idf values, n_tokens, n_kept).
 
     ``stop_words`` must already be case-folded by the caller when caseSensitive=false.
@@ -269,7 +305,7 @@ def featurize_bytes(raw: bytes, stop_words: Sequence[bytes], num_features: int, 
     toks = java_split_ws(b)
     sw = set(stop_words)
     kept = [t for t in toks if t not in sw]
-    idx, tf = hashing_tf(kept, num_features, binary)
+    idx, tf = count_vectorize(kept, vocab_index, binary) if vocab_index is not None else hashing_tf(kept, num_features, binary)
     val = idf_transform(idx, tf, idf) if idf is not None else tf
     return idx, val, len(toks), len(kept)
 
@@ -679,16 +715,17 @@ class OraclePipeline:
     """Feature stages + one classifier, evaluated row by row with the functions above."""
 
     def __init__(self, stop_words: Sequence[str], case_sensitive: bool, num_features: int, binary: bool,
-                 idf: Optional[np.ndarray], classifier: dict):
+                 idf: Optional[np.ndarray], classifier: dict, vocabulary: Optional[Sequence[str]] = None):
         sw = list(stop_words) if case_sensitive else [w.lower() for w in stop_words]
         self.stop_words = [w.encode("utf-8") for w in sw]
         self.num_features = int(num_features)
         self.binary = bool(binary)
         self.idf = None if idf is None else np.asarray(idf, dtype=np.float64)
         self.classifier = classifier  # {"kind": "lr"|"dt"|"rf"|"gbt", ...}
+        self.vocab_index = None if vocabulary is None else {w.encode("utf-8"): i for i, w in enumerate(vocabulary)}
 
     def featurize(self, raw: bytes, do_clean: bool = True):
-        return featurize_bytes(raw, self.stop_words, self.num_features, self.idf, do_clean, self.binary)
+        return featurize_bytes(raw, self.stop_words, self.num_features, self.idf, do_clean, self.binary, self.vocab_index)
 
     def score(self, idx, val):
         c = self.classifier

@@ -17,8 +17,9 @@ def oracle_for(model):
     else:
         trees = [so.Tree(t.feature, t.threshold, t.left, t.right, t.prediction if c.kind == "gbt" else t.stats[:, :2]) for t in c.trees]
         cl = {"kind": c.kind, "trees": trees, "weights": list(c.treeWeights)}
-    return so.OraclePipeline(sw, cs, int(p.hashing.getOrDefault("numFeatures")), bool(p.hashing.getOrDefault("binary")),
-                             p.idf.idf if p.idf is not None else None, cl)
+    vocab = getattr(p.hashing, "vocabulary", None)
+    return so.OraclePipeline(sw, cs, p.num_features, bool(p.hashing.getOrDefault("binary")),
+                             p.idf.idf if p.idf is not None else None, cl, vocabulary=vocab)
 
 
 _WORDS = ["hello", "Hello", "HELLO", "social", "Security", "number", "the", "The", "a", "I", "i'm", "don't", "you're", "is",

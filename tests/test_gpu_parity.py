@@ -285,3 +285,34 @@ def test_many_deferred_dialogues_at_scale(fd):
     rp, ix, vl = co.featurize(pk.data, pk.offs, True)
     assert np.array_equal(rowptr.cpu().numpy(), rp) and np.array_equal(idx.cpu().numpy(), ix) and np.array_equal(val.cpu().numpy(), vl)
     assert (np.diff(rp) > 160).mean() > 0.99
+
+
+@pytest.mark.parametrize("binary", [False, True])
+def test_count_vectorizer_model_transform(fd, binary, tmp_path):
+    """CountVectorizerModel (the reference training script's featuriser, fraud_detection_spark.py:52): dictionary
+    lookup instead of hashing; unknown terms ignored; long terms, the empty term and 20,000 entries."""
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    rng = np.random.default_rng(6)
+    corpus = synth.SynthCorpus(n_words=30000, seed=19)
+    vocab = [w.decode() for w in corpus.words[corpus.n_stop:corpus.n_stop + 19990]]
+    vocab = ["", "hello", "security", "antidisestablishmentarianism", "internationalisation", "social", "winner", "q", "im", "dont"] + vocab
+    rng.shuffle(vocab)
+    idf = np.round(rng.random(len(vocab)) * 4, 4)
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"), fd.StopWordsRemover(inputCol="words", outputCol="filtered_words"),
+              fd.CountVectorizerModel(vocab, inputCol="filtered_words", outputCol="raw_features", binary=binary),
+              fd.IDFModel(idf, inputCol="raw_features", outputCol="features"),
+              fd.LogisticRegressionModel(rng.normal(0, 1, len(vocab)), -0.3, featuresCol="features")]
+    model = fd.PipelineModel(stages)
+    pk, _ = corpus.sample(400, tokens=150, device="cpu", seed=2)
+    d, o = pk.data.numpy(), pk.offs.numpy()
+    rows = [bytes(d[o[i]:o[i + 1]]) for i in range(400)] + [t.encode() for t in messy_texts(300, seed=8)] + [t.encode() for t in _long_rows()[:8]]
+    ora = oracle_for(model)
+    rowptr, idx, val = model.featurize(rows)
+    for t, (ix, vl) in zip(rows, csr_rows(rowptr, idx, val)):
+        eix, evl, _, _ = ora.featurize(t)
+        assert ix == eix and vl == evl, repr(t[:40])
+    _check_scores(model.transform(rows), ora.transform(rows))
+    model.save(str(tmp_path / "cv"))
+    again = fd.PipelineModel.load(str(tmp_path / "cv"))
+    assert again.stages[2].vocabulary == vocab
+    _check_scores(again.transform(rows), ora.transform(rows))
