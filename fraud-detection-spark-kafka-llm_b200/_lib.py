@@ -25,6 +25,7 @@ SIGNATURES = {
     "fd_set_stopwords": (C.c_int, [_p, _p, _p, _i32, _i32]),
     "fd_set_hashing": (C.c_int, [_p, _i32, _i32]),
     "fd_set_vocabulary": (C.c_int, [_p, _p, _p, _i32, _i32]),
+    "fd_vocab_count": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _i32, _p, _i64, _p, _p]),
     "fd_hash_terms": (C.c_int, [_p, _p, _i32, _i32, _p]),
     "fd_set_idf": (C.c_int, [_p, _p, _i32]),
     "fd_set_linear": (C.c_int, [_p, _p, _i32, _f64, _f64]),

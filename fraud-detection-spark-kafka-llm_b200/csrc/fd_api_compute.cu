@@ -204,6 +204,41 @@ int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev,
     return FD_OK;
 }
 
+int fd_vocab_count(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev, int64_t n_rows, uint32_t flags,
+                   uint64_t* keys_dev, uint32_t* info_dev, int32_t log2_slots, uint8_t* pool_dev, int64_t pool_bytes,
+                   uint64_t* counters_dev, void* stream) {
+    if (!h) return FD_ERR_INVALID;
+    if (n_rows < 0 || (n_rows > 0 && (!text_dev || !offs_dev))) return set_err(h, FD_ERR_INVALID, "bad text arguments");
+    if (((uintptr_t)text_dev & 15) != 0) return set_err(h, FD_ERR_INVALID, "text pointer must be 16-byte aligned");
+    if (!keys_dev || !info_dev || !counters_dev || log2_slots < 10 || log2_slots > 30 || pool_bytes < 0 || (pool_bytes > 0 && !pool_dev))
+        return set_err(h, FD_ERR_INVALID, "bad term-table arguments");
+    if (n_rows == 0) return FD_OK;
+    FD_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = ensure_ws(h, slot_bytes(n_rows));
+    if (rc) return rc;
+    RowArgs a;
+    memset(&a, 0, sizeof(a));
+    a.text = text_dev;
+    a.offs = offs_dev;
+    a.n_rows = n_rows;
+    a.flags = flags;
+    a.m = h->m;
+    a.m.vocab_cap = 0;  // counting terms: neither the hashing trick nor an earlier vocabulary applies
+    a.m.binary = 0;
+    a.m.drop_empty = a.m.empty_is_stop;
+    fill_slot(a, h->ws, n_rows);
+    a.fit_keys = reinterpret_cast<unsigned long long*>(keys_dev);
+    a.fit_info = reinterpret_cast<uint4*>(info_dev);
+    a.fit_log2 = log2_slots;
+    a.fit_pool = pool_dev;
+    a.fit_pool_cap = pool_bytes;
+    a.fit_counters = reinterpret_cast<unsigned long long*>(counters_dev);
+    FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, CTRL_CLEAR_BYTES, st));
+    FD_CUDA(h, launch_rows(h, MODE_FIT, a, st));
+    return FD_OK;
+}
+
 int fd_status(fd_handle* h, void* stream) {
     if (!h) return FD_ERR_INVALID;
     if (!h->ws) return FD_OK;

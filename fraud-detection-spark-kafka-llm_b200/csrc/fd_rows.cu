@@ -107,6 +107,61 @@ __device__ uint32_t vocab_index(const Model& m, uint32_t h, uint32_t n, uint32_t
     return NOT_IN_VOCAB;
 }
 
+// CountVectorizer.fit: find-or-create the term in the caller's global table and add `inc` to its term count; returns
+// the slot (the term's identity for the per-document count table).  Terms of up to 7 bytes are identified by their
+// bytes; longer ones by a 56-bit hash (murmur3 x cheap mix) -- a collision there would merge two terms' counts.
+__device__ uint32_t fit_slot(const RowArgs& a, uint32_t h, uint32_t n, uint32_t b0, uint32_t b1, uint32_t b2, const uint8_t* rb,
+                             const uint32_t* lmask, int s, int e, uint32_t inc) {
+    unsigned long long key;
+    if (n <= 7u) key = ((unsigned long long)n << 56) | ((unsigned long long)(b1 & 0x00FFFFFFu) << 32) | b0;
+    else key = 0xFF00000000000000ULL | ((((unsigned long long)h << 24) ^ sw_key(n, b0, b1, b2)) & 0x00FFFFFFFFFFFFFFULL);
+    if (key == ~0ULL) key ^= 1ULL;
+    const uint32_t mask = (1u << a.fit_log2) - 1u;
+    uint32_t slot = (uint32_t)((key * 0x9E3779B97F4A7C15ULL) >> (64 - a.fit_log2));
+    for (uint32_t probes = 0; probes <= mask; ++probes) {
+        const unsigned long long old = atomicCAS(a.fit_keys + slot, ~0ULL, key);
+        if (old == ~0ULL) {  // this thread created the entry: record its bytes for the host
+            atomicAdd(a.fit_counters, 1ULL);
+            uint32_t off = 0xFFFFFFFFu;
+            if (n > 7u && s >= 0) {
+                const unsigned long long o = atomicAdd(a.fit_counters + 1, (unsigned long long)n);
+                if ((long long)(o + n) <= a.fit_pool_cap) {
+                    off = (uint32_t)o;
+                    uint32_t i = 0;
+                    for (int p = s; p < e; ++p)
+                        if ((lmask[p >> 5] >> (p & 31)) & 1u) a.fit_pool[o + i++] = rb[p];
+                } else {
+                    a.fit_counters[2] = 1ULL;
+                }
+            }
+            a.fit_info[slot].z = off;
+            a.fit_info[slot].w = n;
+        }
+        if (old == ~0ULL || old == key) {
+            atomicAdd(&a.fit_info[slot].x, inc);
+            return slot;
+        }
+        slot = (slot + 1u) & mask;
+    }
+    a.fit_counters[2] = 1ULL;  // table full
+    return 0u;
+}
+
+// term -> index of the per-document count table, by mode: hashing trick, vocabulary lookup, or (fit) global term slot
+template <int MODE>
+__device__ __forceinline__ uint32_t term_index(const RowArgs& a, uint32_t h, uint32_t n, uint32_t b0, uint32_t b1, uint32_t b2,
+                                               const uint8_t* rb, const uint32_t* lmask, int s, int e) {
+    if (MODE == MODE_FIT) return fit_slot(a, h, n, b0, b1, b2, rb, lmask, s, e, 1u);
+    return a.m.vocab_cap ? vocab_index(a.m, h, n, b0, b1, b2, rb, lmask, s, e) : feature_index(h, a.m);
+}
+template <int MODE>
+__device__ __forceinline__ uint32_t empty_index(const RowArgs& a, uint32_t inc) {
+    if (MODE == MODE_FIT) return fit_slot(a, 142593372u, 0u, 0u, 0u, 0u, nullptr, nullptr, -1, -1, inc);  // murmur3("") = 142593372
+    return a.m.empty_idx;
+}
+template <int MODE>
+__device__ __forceinline__ bool count_term(const RowArgs& a, unsigned long long* tab, int log2cap, uint32_t fi, uint32_t inc, bool binary);
+
 __device__ __forceinline__ uint32_t tab_slot(uint32_t idx, int log2cap) { return (idx * 0x9E3779B1u) >> (32 - log2cap); }
 
 // (bucket -> count) insert; returns true when the bucket is new for this dialogue
@@ -125,6 +180,13 @@ __device__ __forceinline__ bool tab_insert(unsigned long long* tab, int log2cap,
         }
         slot = (slot + 1u) & mask;
     }
+}
+
+template <int MODE>
+__device__ __forceinline__ bool count_term(const RowArgs& a, unsigned long long* tab, int log2cap, uint32_t fi, uint32_t inc, bool binary) {
+    const bool isnew = tab_insert(tab, log2cap, fi, inc, binary);
+    if (MODE == MODE_FIT && isnew) atomicAdd(&a.fit_info[fi].y, 1u);  // first occurrence in this document
+    return isnew;
 }
 
 __device__ __forceinline__ uint32_t tab_lookup(const unsigned long long* tab, int log2cap, uint32_t idx) {
@@ -432,7 +494,7 @@ k_rows(const RowArgs a) {
             // a letter exists in this window: empties carried from earlier windows were interior
             if (pend && !big && !m.drop_empty) {
                 bool isnew = false;
-                if (lane == 0) isnew = tab_insert(tab, TLOG2, m.empty_idx, pend, binary);
+                if (lane == 0) isnew = count_term<MODE>(a, tab, TLOG2, empty_index<MODE>(a, pend), pend, binary);
                 D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
             }
             pend = 0;
@@ -452,8 +514,8 @@ k_rows(const RowArgs a) {
                         if (gt.n == 0) {
                             was_empty = true;
                         } else if (!(m.sw_cap && is_stop_word(swt, sww, m.sw_cap, h, gt.n, gt.b0, gt.b1, gt.b2))) {
-                            const uint32_t fi = m.vocab_cap ? vocab_index(m, h, gt.n, gt.b0, gt.b1, gt.b2, rb, S.lmask, -1, -1) : feature_index(h, m);
-                            if (fi != NOT_IN_VOCAB) isnew = tab_insert(tab, TLOG2, fi, 1u, binary);
+                            const uint32_t fi = term_index<MODE>(a, h, gt.n, gt.b0, gt.b1, gt.b2, rb, S.lmask, -1, -1);
+                            if (fi != NOT_IN_VOCAB) isnew = count_term<MODE>(a, tab, TLOG2, fi, 1u, binary);
                         }
                         gt.reset();
                     }
@@ -463,7 +525,7 @@ k_rows(const RowArgs a) {
                         // empty multi-window token: interior iff a letter follows in this window
                         if (S.tok[0] <= last_letter) {
                             bool nw2 = false;
-                            if (lane == 0 && !m.drop_empty) nw2 = tab_insert(tab, TLOG2, m.empty_idx, 1u, binary);
+                            if (lane == 0 && !m.drop_empty) nw2 = count_term<MODE>(a, tab, TLOG2, empty_index<MODE>(a, 1u), 1u, binary);
                             D += __popc(__ballot_sync(0xFFFFFFFFu, nw2));
                         } else {
                             pend += 1;
@@ -586,13 +648,13 @@ k_rows(const RowArgs a) {
                 for (int u = 0; u < TPL; ++u) {
                     const bool interior_empty = empty[u] && s[u] <= last_letter;
                     bool ins = valid[u] && (empty[u] ? (interior_empty && !m.drop_empty) : !stop[u]);
-                    uint32_t fi = m.empty_idx;
-                    if (ins && !empty[u]) {
-                        fi = m.vocab_cap ? vocab_index(m, h[u], n[u], b0[u], b1[u], b2[u], rb, S.lmask, s[u], e[u]) : feature_index(h[u], m);
+                    uint32_t fi = 0u;
+                    if (ins) {
+                        fi = empty[u] ? empty_index<MODE>(a, 1u) : term_index<MODE>(a, h[u], n[u], b0[u], b1[u], b2[u], rb, S.lmask, s[u], e[u]);
                         ins = fi != NOT_IN_VOCAB;
                     }
                     bool isnew = false;
-                    if (ins) isnew = tab_insert(tab, TLOG2, fi, 1u, binary);
+                    if (ins) isnew = count_term<MODE>(a, tab, TLOG2, fi, 1u, binary);
                     D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
                     pend += __popc(__ballot_sync(0xFFFFFFFFu, empty[u] && !interior_empty));
                 }
@@ -606,7 +668,7 @@ k_rows(const RowArgs a) {
             if (!big && row_sp == 0 && !row_letter && !m.drop_empty) {
                 // no separator anywhere and nothing kept: Java's split returns [""] -- one empty token
                 bool isnew = false;
-                if (lane == 0) isnew = tab_insert(tab, TLOG2, m.empty_idx, 1u, binary);
+                if (lane == 0) isnew = count_term<MODE>(a, tab, TLOG2, empty_index<MODE>(a, 1u), 1u, binary);
                 D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
             }
             __syncwarp();
@@ -983,6 +1045,7 @@ cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int me
         case MODE_DT: FD_DISPATCH(MODE_DT);
         case MODE_RF: FD_DISPATCH(MODE_RF);
         case MODE_GBT: FD_DISPATCH(MODE_GBT);
+        case MODE_FIT: FD_DISPATCH(MODE_FIT);
     }
 #undef FD_DISPATCH
     return cudaErrorInvalidValue;

@@ -28,7 +28,7 @@ constexpr size_t wide_pool_slots(int med_ctas, int big_workers) {
                                                                                          : ((size_t)big_workers << BIG_LOG2);
 }
 
-enum Mode { MODE_CSR = 0, MODE_LINEAR = 1, MODE_DT = 2, MODE_RF = 3, MODE_GBT = 4 };
+enum Mode { MODE_CSR = 0, MODE_LINEAR = 1, MODE_DT = 2, MODE_RF = 3, MODE_GBT = 4, MODE_FIT = 5 };
 
 template <int TL>
 struct __align__(16) WarpSmem {
@@ -56,6 +56,13 @@ struct RowArgs {
     long long* row_tmpoff;
     unsigned long long* tmp;
     long long tmp_cap;
+    // CountVectorizer.fit (MODE_FIT): global term table owned by the caller
+    unsigned long long* fit_keys;   // [1 << fit_log2], ~0 = empty
+    uint4* fit_info;                // per slot: x = term count, y = document frequency, z = pool offset, w = length
+    int fit_log2;
+    uint8_t* fit_pool;              // bytes of terms longer than 7 bytes
+    long long fit_pool_cap;
+    unsigned long long* fit_counters;  // [0] = entries, [1] = pool bytes used, [2] = overflow flag
     // score outputs
     double* pred;
     double* prob;

@@ -373,13 +373,21 @@ class Pipeline:
     def fit(self, batch, labels=None, cleaned: Optional[bool] = None, device: Optional[int] = None, **explicit) -> PipelineModel:
         torch = _torch()
         import torch.distributed as dist
-        feats = [s for s in self.stages if isinstance(s, (S.Tokenizer, S.StopWordsRemover, S.HashingTF))]
+        feats = [s for s in self.stages if isinstance(s, (S.Tokenizer, S.StopWordsRemover, S.HashingTF, S.CountVectorizer, S.CountVectorizerModel))]
         idf = [s for s in self.stages if isinstance(s, (S.IDF, S.IDFModel))]
         est = [s for s in self.stages if isinstance(s, (S._TreeEstimator, S.ClassificationModel))]
         if len(idf) > 1 or len(est) > 1 or len(feats) + len(idf) + len(est) != len(self.stages):
             raise ValueError("unsupported pipeline shape for the B200 path")
         if isinstance(batch, dict) and labels is None and est:
             labels = batch[est[0].getOrDefault("labelCol")]
+        for i, st in enumerate(feats):
+            if isinstance(st, S.CountVectorizer):  # fit the vocabulary on the device, from the stages before it
+                pre = PipelineModel(feats[:i] + [S.HashingTF(inputCol=st.getOrDefault("inputCol"), outputCol=st.getOrDefault("outputCol"))])
+                pk, flags = pre._packed(batch, cleaned)
+                hnd = pre.handle(device)
+                pk = pk.to_device(torch.device("cuda", hnd.device))
+                feats[i] = st.fit_packed(hnd, pk, flags)
+                batch, cleaned = pk, not bool(flags & _lib.FD_FLAG_CLEAN)
         tf_model = PipelineModel(feats)
         rowptr, idx, val = tf_model.featurize(batch, cleaned=cleaned, device=device)
         dev = rowptr.device

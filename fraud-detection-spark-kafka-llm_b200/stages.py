@@ -161,6 +161,75 @@ class CountVectorizer(Stage):
         self.defaultParamMap = {"outputCol": self.uid + "__output", "vocabSize": 262144, "minDF": 1.0,
                                 "maxDF": 9.223372036854776e18, "minTF": 1.0, "binary": False}
 
+    def fit_packed(self, handle, packed, flags: int) -> CountVectorizerModel:
+        """Count terms over this rank's packed dialogues on the device (``fd_vocab_count``), merge the per-rank
+        tables when a process group is initialised, and keep the ``vocabSize`` most frequent terms that pass
+        minDF / maxDF.  Count ties go to the smaller term bytes (Spark leaves them to partition order)."""
+        import ctypes as C
+
+        import torch
+        import torch.distributed as dist
+
+        from . import _lib
+        dev = packed.data.device
+        n = packed.n_rows
+        total_bytes = int((packed.offs[-1] - packed.offs[0]).item()) if n else 0
+        log2 = max(12, min(28, int(np.ceil(np.log2(max(4096, total_bytes // 16))))))
+        pool_bytes = max(1 << 16, total_bytes // 8)
+        st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        while True:
+            keys = torch.full((1 << log2,), -1, dtype=torch.int64, device=dev)
+            info = torch.zeros((1 << log2, 4), dtype=torch.int32, device=dev)
+            pool = torch.zeros(pool_bytes, dtype=torch.uint8, device=dev)
+            counters = torch.zeros(3, dtype=torch.int64, device=dev)
+            handle.call("fd_vocab_count", _lib.ptr(packed.data), _lib.ptr(packed.offs), n, int(flags), _lib.ptr(keys), _lib.ptr(info), log2,
+                        _lib.ptr(pool), pool_bytes, _lib.ptr(counters), st)
+            handle.call("fd_status", st)
+            entries, used, overflow = (int(x) for x in counters.tolist())
+            if not overflow and entries <= 0.6 * (1 << log2):
+                break
+            if used > pool_bytes:
+                pool_bytes = used + (1 << 16)
+            if overflow and used <= pool_bytes or entries > 0.6 * (1 << log2):
+                log2 += 2
+            if log2 > 30:
+                raise RuntimeError("too many distinct terms for the term table")
+        occ = torch.nonzero(keys != -1).flatten()
+        k = keys[occ].cpu().numpy().view(np.uint64)
+        inf = info[occ].cpu().numpy().view(np.uint32)
+        pool_h = pool[:max(used, 1)].cpu().numpy()
+        terms = {}
+        for key, (cnt, df, off, ln) in zip(k.tolist(), inf.tolist()):
+            if ln <= 7:
+                b = int(key & ((1 << 56) - 1)).to_bytes(7, "little")[:ln]
+            elif off == 0xFFFFFFFF:
+                continue  # a term longer than a staging window: not representable (documented limit)
+            else:
+                b = bytes(pool_h[off:off + ln])
+            terms[b] = (cnt, df)
+        n_docs = n
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            parts = [None] * dist.get_world_size()
+            dist.all_gather_object(parts, (terms, n))
+            terms, n_docs = {}, 0
+            for t, nd in parts:
+                n_docs += nd
+                for b, (c, d) in t.items():
+                    c0, d0 = terms.get(b, (0, 0))
+                    terms[b] = (c0 + c, d0 + d)
+        g = self.getOrDefault
+        min_df, max_df = float(g("minDF")), float(g("maxDF"))
+        lo = min_df if min_df >= 1.0 else min_df * n_docs
+        hi = max_df if max_df >= 1.0 else max_df * n_docs
+        keep = [b for b, (c, d) in terms.items() if lo <= d <= hi] if ("minDF" in self.paramMap or "maxDF" in self.paramMap) else list(terms)
+        keep.sort(key=lambda b: (-terms[b][0], b))
+        vocab = [b.decode("utf-8", "replace") for b in keep[:int(g("vocabSize"))]]
+        if not vocab:
+            raise ValueError("The vocabulary size should be > 0. Lower minDF as necessary.")
+        model = self.model_from_vocabulary(vocab)
+        model.term_counts = {b: terms[b] for b in keep[:int(g("vocabSize"))]}
+        return model
+
     def model_from_vocabulary(self, vocabulary: Sequence[str]) -> CountVectorizerModel:
         m = CountVectorizerModel(vocabulary, uid=self.uid)
         m.paramMap = dict(self.paramMap)

@@ -74,6 +74,18 @@ int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary);
  * Terms outside the vocabulary are ignored, numFeatures becomes n_words; only minTF = 1.0 semantics are implemented.
  * A later fd_set_hashing switches back to HashingTF. */
 int fd_set_vocabulary(fd_handle* h, const uint8_t* words, const int32_t* offs, int32_t n_words, int32_t binary);
+/* CountVectorizer.fit, counting part (fraud_detection_spark.py:52 via Pipeline.fit at :85-91): tokenise the dialogues
+ * exactly as fd_featurize does (cleaning flag, stop words) and accumulate every surviving term into a caller-owned
+ * open-addressed table in device memory, so that several calls (batches, or ranks merged later) add up:
+ *   keys  u64[1 << log2_slots]   initialised to all ones (empty); terms of <= 7 bytes are stored as their bytes
+ *                                (length in the top byte), longer ones as 0xFF + a 56-bit hash
+ *   info  u32[1 << log2_slots][4] initialised to zero: {term count, document frequency, pool offset, length}
+ *   pool  u8[pool_bytes]          bytes of the terms longer than 7 bytes (offset 0xFFFFFFFF: not recorded)
+ *   counters u64[3]               initialised to zero: {entries, pool bytes used, overflow flag}
+ * The caller picks the vocabulary (top vocabSize by count, minDF / maxDF) from the table.  Asynchronous. */
+int fd_vocab_count(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev, int64_t n_rows, uint32_t flags,
+                   uint64_t* keys_dev, uint32_t* info_dev, int32_t log2_slots, uint8_t* pool_dev, int64_t pool_bytes,
+                   uint64_t* counters_dev, void* stream);
 /* HashingTF.indexOf(term) for n terms on the HOST (no device work): out[i] = nonNegativeMod(
  * murmur3_x86_32(term_i bytes, seed 42), num_features).  terms = bytes back to back, offs int32[n+1]. */
 int fd_hash_terms(const uint8_t* terms, const int32_t* offs, int32_t n, int32_t num_features, int32_t* out);

@@ -166,3 +166,46 @@ def test_decision_tree_pipeline_matches_oracle_end_to_end(fd):
     tf_rows = [so.featurize_bytes(t.encode(), ora.stop_words, nf, None)[:2] for t in texts]
     idf, df, m = so.idf_fit(tf_rows, nf)
     assert np.array_equal(idf.view(np.uint64), model.stages[3].idf.view(np.uint64)) and m == 900
+
+
+def test_count_vectorizer_fit_and_reference_training_pipeline(fd, tmp_path):
+    """The reference's own training pipeline shape (fraud_detection_spark.py:47-65): Tokenizer -> StopWordsRemover ->
+    CountVectorizer(vocabSize) -> IDF -> DecisionTreeClassifier, fitted end to end on the GPU.  The vocabulary (terms,
+    total counts, document frequencies) is checked against the oracle's CountVectorizer.fit."""
+    from helpers import oracle_for
+    from oracle import spark_oracle as so
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    corpus = synth.SynthCorpus(n_words=3000, seed=23)
+    planted = {"ids": list(range(corpus.n_stop + 50, corpus.n_stop + 58)), "rate": 0.1}
+    pk, lab = corpus.sample(1500, tokens=80, device="cpu", seed=6, planted=planted)
+    data, offs = pk.data.numpy(), pk.offs.numpy()
+    texts = [bytes(data[offs[i]:offs[i + 1]]).decode() for i in range(1500)]
+    texts[3] = "Hello, WORLD!! internationalisation antidisestablishmentarianism  hello the the"
+    texts[4] = ""
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"), fd.StopWordsRemover(inputCol="words", outputCol="filtered_words"),
+              fd.CountVectorizer(inputCol="filtered_words", outputCol="raw_features", vocabSize=500),
+              fd.IDF(inputCol="raw_features", outputCol="features"),
+              fd.DecisionTreeClassifier(featuresCol="features", labelCol="labels", maxDepth=5)]
+    model = fd.Pipeline(stages=stages).fit(texts, labels=lab.numpy())
+    cv = model.stages[2]
+    assert type(cv).__name__ == "CountVectorizerModel" and len(cv.vocabulary) == 500
+    sw = [w.encode() for w in model.stages[1].getOrDefault("stopWords")]
+    docs = [[t for t in so.java_split_ws(so.clean_bytes(x.encode())) if t not in set(sw)] for x in texts]
+    vocab, tc, df = so.count_vectorizer_fit(docs, 500)
+    assert [v.encode() for v in cv.vocabulary] == vocab
+    for b, (c, d) in cv.term_counts.items():
+        assert (c, d) == (tc[b], df[b]), b
+    assert b"" in tc  # the empty token is a term like any other
+    # the fitted pipeline scores like the oracle built from the same stages
+    ora = oracle_for(model)
+    res = model.transform(texts)
+    exp = ora.transform([t.encode() for t in texts])
+    assert np.array_equal(res["prediction"].cpu().numpy(), exp[0]) and np.array_equal(res["rawPrediction"].cpu().numpy(), exp[2])
+    model.save(str(tmp_path / "ref_shape"))
+    again = fd.PipelineModel.load(str(tmp_path / "ref_shape"))
+    assert again.stages[2].vocabulary == cv.vocabulary and torch.equal(again.transform(texts)["prediction"], res["prediction"])
+    # minDF filters by document frequency
+    cv2 = fd.CountVectorizer(inputCol="filtered_words", outputCol="raw_features", vocabSize=100000, minDF=3.0)
+    m2 = fd.Pipeline(stages=[stages[0], stages[1], cv2]).fit(texts)
+    exp2, _, _ = so.count_vectorizer_fit(docs, 100000, min_df=3.0)
+    assert [v.encode() for v in m2.stages[2].vocabulary] == exp2
