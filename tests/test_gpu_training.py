@@ -2,6 +2,7 @@
 bins, bag weights and feature subsets (identical splits on identical bins -- BASELINE.json north_star), and
 Pipeline.fit produces a model whose held-out AUC shows the planted signal."""
 import importlib
+import os
 
 import numpy as np
 import pytest
@@ -209,3 +210,17 @@ def test_count_vectorizer_fit_and_reference_training_pipeline(fd, tmp_path):
     m2 = fd.Pipeline(stages=[stages[0], stages[1], cv2]).fit(texts)
     exp2, _, _ = so.count_vectorizer_fit(docs, 100000, min_df=3.0)
     assert [v.encode() for v in m2.stages[2].vocabulary] == exp2
+
+
+def test_reference_trainer_flow_example(fd, tmp_path):
+    """examples/fraud_detection_b200.py = the reference's fraud_detection_spark.py main flow on this stack."""
+    import runpy
+    mod = runpy.run_path(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples", "fraud_detection_b200.py"))
+    report, models = mod["main"](["--rows", "1600", "--trees", "20", "--save", str(tmp_path / "fraud_detection_model")])
+    for name in ("DecisionTree", "RandomForest"):
+        m = report[name]["Test"]["metrics"]
+        lo_auc, lo_acc = (0.9, 0.85) if name == "RandomForest" else (0.75, 0.7)  # one depth-5 tree on 20 planted words
+        assert m["AUC"] > lo_auc and m["Accuracy"] > lo_acc, (name, m)
+        assert report[name]["Test"]["confusion_matrix"].sum() > 200
+    saved = fd.PipelineModel.load(str(tmp_path / "fraud_detection_model"))
+    assert [type(s).__name__ for s in saved.stages] == ["Tokenizer", "StopWordsRemover", "CountVectorizerModel", "IDFModel", "DecisionTreeClassificationModel"]
