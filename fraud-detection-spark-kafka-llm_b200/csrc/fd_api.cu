@@ -177,6 +177,7 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
         m.sw_pool = nullptr;
         m.sw_cap = 0;
         m.n_sw = 0;
+        m.sw_perfect = 0;
         return FD_OK;
     }
     if (n_words > 2048) return set_err(h, FD_ERR_LIMIT, "at most 2048 stop words are supported (got %d)", n_words);
@@ -215,32 +216,61 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
         wordsv.push_back(s);
         hashes.push_back(murmur3_host(w.data(), len));
     }
-    int cap = 64;
-    while (cap < 4 * (int)wordsv.size()) cap <<= 1;
+    // first choice: a perfect hash (one probe on the device) -- look for a multiplier that spreads the words' murmur
+    // hashes over 2^11 or 2^12 sixteen-bit slots without any collision; feasible for a few hundred words
     std::vector<uint32_t> tab;
-    for (;; cap <<= 1) {
-        if (cap > (1 << 16)) return set_err(h, FD_ERR_LIMIT, "could not place the stop words in the lookup table");
-        tab.assign(cap, 0u);
-        const uint32_t mask = (uint32_t)cap - 1u;
-        bool ok = true;
-        for (size_t i = 0; i < wordsv.size() && ok; ++i) {
-            uint32_t id = (uint32_t)i;
-            uint32_t slot = hashes[id] & mask;
-            ok = false;
-            for (int kick = 0; kick < 512; ++kick) {
-                if (tab[slot] == 0u) {
-                    tab[slot] = (hashes[id] & 0xFFFF0000u) | (id + 1u);
-                    ok = true;
-                    break;
-                }
-                const uint32_t other = (tab[slot] & 0xFFFFu) - 1u;  // evict the resident to its alternate slot
-                tab[slot] = (hashes[id] & 0xFFFF0000u) | (id + 1u);
-                id = other;
-                const uint32_t s1 = hashes[id] & mask, s2 = (hashes[id] >> 10) & mask;
-                slot = (slot == s1) ? s2 : s1;
+    int cap = 0;
+    m.sw_perfect = 0;
+    for (int lg = 11; lg <= 12 && !m.sw_perfect && wordsv.size() <= 400; ++lg) {
+        std::vector<uint16_t> t16((size_t)1 << lg);
+        uint64_t x = 0x9E3779B97F4A7C15ULL;
+        for (int trial = 0; trial < (lg == 11 ? 60000 : 400000) && !m.sw_perfect; ++trial) {
+            x ^= x >> 12; x ^= x << 25; x ^= x >> 27;            // xorshift64*
+            const uint32_t mul = (uint32_t)((x * 0x2545F4914F6CDD1DULL) >> 32) | 1u;
+            std::fill(t16.begin(), t16.end(), (uint16_t)0);
+            bool ok = true;
+            for (size_t i = 0; i < wordsv.size() && ok; ++i) {
+                const uint32_t slot = (hashes[i] * mul) >> (32 - lg);
+                ok = t16[slot] == 0;
+                t16[slot] = (uint16_t)(i + 1);
+            }
+            if (ok) {
+                m.sw_perfect = 1;
+                m.sw_mul = mul;
+                m.sw_shift = 32 - lg;
+                cap = 1 << lg;
+                tab.assign((size_t)cap / 2, 0u);
+                memcpy(tab.data(), t16.data(), (size_t)cap * 2);
             }
         }
-        if (ok) break;
+    }
+    if (!m.sw_perfect) {
+        cap = 64;
+        while (cap < 4 * (int)wordsv.size()) cap <<= 1;
+        for (;; cap <<= 1) {
+            if (cap > (1 << 16)) return set_err(h, FD_ERR_LIMIT, "could not place the stop words in the lookup table");
+            tab.assign(cap, 0u);
+            const uint32_t mask = (uint32_t)cap - 1u;
+            bool ok = true;
+            for (size_t i = 0; i < wordsv.size() && ok; ++i) {
+                uint32_t id = (uint32_t)i;
+                uint32_t slot = hashes[id] & mask;
+                ok = false;
+                for (int kick = 0; kick < 512; ++kick) {
+                    if (tab[slot] == 0u) {
+                        tab[slot] = (hashes[id] & 0xFFFF0000u) | (id + 1u);
+                        ok = true;
+                        break;
+                    }
+                    const uint32_t other = (tab[slot] & 0xFFFFu) - 1u;  // evict the resident to its alternate slot
+                    tab[slot] = (hashes[id] & 0xFFFF0000u) | (id + 1u);
+                    id = other;
+                    const uint32_t s1 = hashes[id] & mask, s2 = (hashes[id] >> 10) & mask;
+                    slot = (slot == s1) ? s2 : s1;
+                }
+            }
+            if (ok) break;
+        }
     }
     int rc = upload(h, &m.sw_tab, tab.data(), tab.size());
     if (rc) return rc;

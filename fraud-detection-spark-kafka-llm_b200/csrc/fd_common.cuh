@@ -37,10 +37,16 @@ struct Ctrl {
 };
 
 struct Model {
-    __host__ __device__ size_t sw_smem_bytes() const { return (size_t)sw_cap * 4 + (size_t)n_sw * 16; }
+    __host__ __device__ size_t sw_tab_bytes() const { return sw_perfect ? (size_t)sw_cap * 2 : (size_t)sw_cap * 4; }
+    __host__ __device__ size_t sw_smem_bytes() const { return sw_tab_bytes() + (size_t)n_sw * 16; }
     // stop words: 2-choice cuckoo table of 4-byte slots keyed by murmur3(word, 42): a word sits at slot
     //   h & mask or (h >> 10) & mask; slot = (hash & 0xFFFF0000) | (word id + 1), 0 = empty
     uint32_t* sw_tab = nullptr;
+    // perfect-hash mode (found on the host for lists of a few hundred words): ONE probe -- 16-bit slots holding
+    // word id + 1 at index (h * sw_mul) >> sw_shift, no two words share a slot; otherwise the cuckoo layout above
+    int sw_perfect = 0;
+    uint32_t sw_mul = 0;
+    int sw_shift = 0;
     int sw_cap = 0;             // slots, power of two, 0 = no stop words
     uint4* sw_words = nullptr;  // per word: x = len (|0x80000000 when > 12 bytes), y/z/w = first 12 bytes or y = pool offset
     int n_sw = 0;

@@ -245,9 +245,15 @@ __device__ __noinline__ bool long_stop_word_equal(const uint8_t* word, const uin
 
 // is the multi-window token (hash h, n kept bytes, first 12 bytes b0..b2) a stop word?  (words longer than 12
 // bytes are not matched on this rare path -- documented limitation)
-__device__ bool is_stop_word(const uint32_t* swt, const uint4* sww, int sw_cap, uint32_t h, uint32_t n, uint32_t b0,
+__device__ bool is_stop_word(const Model& m, const uint32_t* swt, const uint4* sww, uint32_t h, uint32_t n, uint32_t b0,
                              uint32_t b1, uint32_t b2) {
-    const uint32_t mask = (uint32_t)sw_cap - 1u;
+    if (m.sw_perfect) {
+        const uint32_t id = reinterpret_cast<const uint16_t*>(swt)[(h * m.sw_mul) >> m.sw_shift];
+        if (!id) return false;
+        const uint4 w = sww[id - 1u];
+        return w.x == n && w.y == b0 && w.z == b1 && w.w == b2;
+    }
+    const uint32_t mask = (uint32_t)m.sw_cap - 1u;
     const uint32_t cand[2] = {swt[h & mask], swt[(h >> 10) & mask]};
     for (int i = 0; i < 2; ++i) {
         const uint32_t e = cand[i];
@@ -281,13 +287,13 @@ k_rows(const RowArgs a) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const Model& m = a.m;
-    uint4* sww = reinterpret_cast<uint4*>(smem_raw + (size_t)m.sw_cap * 4);
+    uint4* sww = reinterpret_cast<uint4*>(smem_raw + m.sw_tab_bytes());
     WarpSmemT& S = *reinterpret_cast<WarpSmemT*>(smem_raw + m.sw_smem_bytes() + (size_t)warp * sizeof(WarpSmemT));
 
     if (BIG && (long long)blockIdx.x * ROW_WARPS >= (long long)(BIG == 1 ? a.ctrl->big_count : a.ctrl->big2_count))
         return;  // nothing deferred to this CTA
     if (!BIG && a.pick_shape && a.ctrl->shape != TL) return;  // the other shape was picked for this call
-    for (int i = threadIdx.x; i < m.sw_cap; i += blockDim.x) swt[i] = m.sw_tab[i];
+    for (int i = threadIdx.x; i < (int)(m.sw_tab_bytes() / 4); i += blockDim.x) swt[i] = m.sw_tab[i];
     for (int i = threadIdx.x; i < m.n_sw; i += blockDim.x) sww[i] = m.sw_words[i];
     if (lane == 0) {
         mbar_init(&S.mbar[0], 1);
@@ -513,7 +519,7 @@ k_rows(const RowArgs a) {
                         const uint32_t h = gt.finish();
                         if (gt.n == 0) {
                             was_empty = true;
-                        } else if (!(m.sw_cap && is_stop_word(swt, sww, m.sw_cap, h, gt.n, gt.b0, gt.b1, gt.b2))) {
+                        } else if (!(m.sw_cap && is_stop_word(m, swt, sww, h, gt.n, gt.b0, gt.b1, gt.b2))) {
                             const uint32_t fi = term_index<MODE>(a, h, gt.n, gt.b0, gt.b1, gt.b2, rb, S.lmask, -1, -1);
                             if (fi != NOT_IN_VOCAB) isnew = count_term<MODE>(a, tab, TLOG2, fi, 1u, binary);
                         }
@@ -625,7 +631,15 @@ k_rows(const RowArgs a) {
 #pragma unroll
                 for (int u = 0; u < TPL; ++u) {
                     stop[u] = false;
-                    if (m.sw_cap) {
+                    if (m.sw_perfect) {  // one probe: 16-bit slot -> word id, then the record is compared
+                        const uint32_t id = reinterpret_cast<const uint16_t*>(swt)[(h[u] * m.sw_mul) >> m.sw_shift];
+                        if (valid[u] && !empty[u] && id) {
+                            const uint4 w = sww[id - 1u];
+                            stop[u] = (w.x == n[u]) && (w.y == b0[u] && w.z == b1[u] && w.w == b2[u]);
+                            if ((w.x & 0x7FFFFFFFu) == n[u] && (w.x & 0x80000000u))
+                                stop[u] = long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s[u], e[u]);
+                        }
+                    } else if (m.sw_cap) {
                         const uint32_t e1 = swt[h[u] & swmask], e2 = swt[(h[u] >> 10) & swmask];
                         const bool m1 = e1 != 0u && ((e1 ^ h[u]) >> 16) == 0u, m2 = e2 != 0u && ((e2 ^ h[u]) >> 16) == 0u;
                         if (valid[u] && !empty[u] && (m1 || m2)) {
