@@ -737,7 +737,60 @@ k_rows(const RowArgs a) {
 // end-of-dialogue epilogues
 // ------------------------------------------------------------------------------------------------
 // compact the table in place to entries [0, n) and bitonic-sort them ascending by bucket
-__device__ int compact_and_sort(unsigned long long* tab, int log2cap, int lane) {
+// bitonic sort of 32*K packed keys held K per lane (element e = lane*K + r), ascending
+template <int K>
+__device__ __forceinline__ void bitonic_regs(uint32_t (&v)[K], int lane) {
+    constexpr int P = 32 * K;
+#pragma unroll
+    for (int k = 2; k <= P; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= K) {  // partner element lives in lane ^ (j / K), same r
+#pragma unroll
+                for (int r = 0; r < K; ++r) {
+                    const uint32_t o = __shfl_xor_sync(0xFFFFFFFFu, v[r], j / K);
+                    const int e = lane * K + r;
+                    const bool keep_min = ((e & j) == 0) == ((e & k) == 0);
+                    v[r] = keep_min ? min(v[r], o) : max(v[r], o);
+                }
+            } else {  // partner in the same lane
+#pragma unroll
+                for (int r = 0; r < K; ++r) {
+                    if ((r ^ j) > r) {
+                        const int e = lane * K + r;
+                        const bool asc = (e & k) == 0;
+                        const uint32_t x = v[r], y = v[r ^ j];
+                        v[r] = asc ? min(x, y) : max(x, y);
+                        v[r ^ j] = asc ? max(x, y) : min(x, y);
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <int K>
+__device__ __noinline__ void sort_perm_k(const unsigned long long* tab, int n, uint16_t* perm, int lane) {
+    uint32_t v[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        const int e = lane * K + r;
+        v[r] = e < n ? (((uint32_t)(tab[e] >> 32) << 9) | (uint32_t)e) : 0xFFFFFFFFu;  // (bucket, position)
+    }
+    bitonic_regs<K>(v, lane);
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        const int e = lane * K + r;
+        if (e < n) perm[e] = (uint16_t)(v[r] & 511u);
+    }
+}
+
+// compact the table in place to entries [0, n); then order them ascending by bucket.  Small tables (n <= 512, buckets
+// below 2^23) are sorted in REGISTERS -- packed (bucket << 9 | position) keys, one shuffle per compare-exchange -- and
+// the order is returned through perm[] (entry i of the sorted sequence is tab[perm[i]]); otherwise the entries
+// themselves are bitonic-sorted in place and perm is the identity (returned as nullptr).
+__device__ int compact_and_sort(unsigned long long* tab, int log2cap, int lane, bool small_keys, uint16_t* perm_buf,
+                                const uint16_t** perm_out) {
     const int cap = 1 << log2cap;
     int w = 0;
     for (int base = 0; base < cap; base += 32) {
@@ -750,6 +803,18 @@ __device__ int compact_and_sort(unsigned long long* tab, int log2cap, int lane) 
         __syncwarp();
     }
     const int n = w;
+    *perm_out = nullptr;
+    if (n <= 1) return n;
+    if (small_keys && n <= 512) {
+        if (n <= 32) sort_perm_k<1>(tab, n, perm_buf, lane);
+        else if (n <= 64) sort_perm_k<2>(tab, n, perm_buf, lane);
+        else if (n <= 128) sort_perm_k<4>(tab, n, perm_buf, lane);
+        else if (n <= 256) sort_perm_k<8>(tab, n, perm_buf, lane);
+        else sort_perm_k<16>(tab, n, perm_buf, lane);
+        __syncwarp();
+        *perm_out = perm_buf;
+        return n;
+    }
     int P = 1;
     while (P < n) P <<= 1;
     for (int i = n + lane; i < P; i += 32) tab[i] = ~0ULL;
@@ -824,13 +889,17 @@ template <int MODE>
 __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long long* tab, int log2cap, long long row, int D,
                              int lane) {
     const Model& m = a.m;  // scratch: 64 doubles of warp scratch (the token list, free at this point)
+    // sorted order of the compacted entries: tab[perm[i]] (register sort) or tab[i] (in-place sort)
+    uint16_t* perm_buf = reinterpret_cast<uint16_t*>(scratch) + 512;  // second KiB of the token-list area
+    const uint16_t* perm = nullptr;
+    const bool small_keys = m.num_features <= (1 << 23);
     if (MODE == MODE_CSR) {
-        D = compact_and_sort(tab, log2cap, lane);
+        D = compact_and_sort(tab, log2cap, lane, small_keys, perm_buf, &perm);
         unsigned long long pos = 0;
         if (lane == 0) pos = atomicAdd(&a.ctrl->tmp_cursor, (unsigned long long)D);
         pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
         if ((long long)(pos + D) <= a.tmp_cap) {
-            for (int i = lane; i < D; i += 32) a.tmp[pos + i] = tab[i];
+            for (int i = lane; i < D; i += 32) a.tmp[pos + i] = tab[perm ? perm[i] : i];
         } else if (lane == 0) {
             a.ctrl->tmp_overflow = 1u;
         }
@@ -839,12 +908,12 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
             a.row_tmpoff[row] = (long long)pos;
         }
     } else if (MODE == MODE_LINEAR) {
-        D = compact_and_sort(tab, log2cap, lane);
+        D = compact_and_sort(tab, log2cap, lane, small_keys, perm_buf, &perm);
         double sum = 0.0;
         for (int b = 0; b < D; b += 32) {
             const int i = b + lane;
             if (i < D) {
-                const unsigned long long e = tab[i];
+                const unsigned long long e = tab[perm ? perm[i] : i];
                 const uint32_t idx = (uint32_t)(e >> 32);
                 scratch[lane] = __dmul_rn(feat_value(m, idx, (uint32_t)e), __ldg(m.coef + idx));
             }
