@@ -885,6 +885,19 @@ __device__ __forceinline__ int walk_tree(const Model& m, const unsigned long lon
     }
 }
 
+// acc + src[0] + src[1] + ... + src[cnt-1], strictly left to right (the order Spark's loops add in); src is 16-byte
+// aligned shared memory, read two doubles per load
+__device__ __forceinline__ double ordered_sum(double acc, const double* src, int cnt) {
+    int l = 0;
+    for (; l + 1 < cnt; l += 2) {
+        const double2 v = *reinterpret_cast<const double2*>(src + l);
+        acc = __dadd_rn(acc, v.x);
+        acc = __dadd_rn(acc, v.y);
+    }
+    if (l < cnt) acc = __dadd_rn(acc, src[l]);
+    return acc;
+}
+
 template <int MODE>
 __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long long* tab, int log2cap, long long row, int D,
                              int lane) {
@@ -918,10 +931,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
                 scratch[lane] = __dmul_rn(feat_value(m, idx, (uint32_t)e), __ldg(m.coef + idx));
             }
             __syncwarp();
-            if (lane == 0) {
-                const int cnt = min(32, D - b);
-                for (int l = 0; l < cnt; ++l) sum = __dadd_rn(sum, scratch[l]);
-            }
+            if (lane == 0) sum = ordered_sum(sum, scratch, min(32, D - b));
             __syncwarp();
         }
         sum = __shfl_sync(0xFFFFFFFFu, sum, 0);
@@ -945,11 +955,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
                 scratch[32 + lane] = st.y;
             }
             __syncwarp();
-            if (lane < 2) {
-                const int cnt = min(32, m.n_trees - b);
-                const double* src = scratch + 32 * lane;
-                for (int l = 0; l < cnt; ++l) v = __dadd_rn(v, src[l]);
-            }
+            if (lane < 2) v = ordered_sum(v, scratch + 32 * lane, min(32, m.n_trees - b));
             __syncwarp();
         }
         const double v0 = __shfl_sync(0xFFFFFFFFu, v, 0), v1 = __shfl_sync(0xFFFFFFFFu, v, 1);
@@ -966,10 +972,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
                 scratch[lane] = __dmul_rn(leaf.thr, __ldg(m.tree_w + t));
             }
             __syncwarp();
-            if (lane == 0) {
-                const int cnt = min(32, m.n_trees - b);
-                for (int l = 0; l < cnt; ++l) mg = __dadd_rn(mg, scratch[l]);
-            }
+            if (lane == 0) mg = ordered_sum(mg, scratch, min(32, m.n_trees - b));
             __syncwarp();
         }
         mg = __shfl_sync(0xFFFFFFFFu, mg, 0);
