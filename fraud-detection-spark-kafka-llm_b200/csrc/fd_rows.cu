@@ -368,13 +368,14 @@ k_rows(const RowArgs a) {
         }
 
         // ================= pass A: classify 32 bytes per lane =================
-        uint32_t L = 0, SP = 0;
+        uint32_t L = 0, SP = 0, vmask_all = 0;
         {
             uint4 q0 = *reinterpret_cast<const uint4*>(rb + 32 * lane);
             uint4 q1 = *reinterpret_cast<const uint4*>(rb + 32 * lane + 16);
             uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
             const int lo_l = min(max(lo - 32 * lane, 0), 32), hi_l = min(max(hi - 32 * lane, 0), 32);
             const uint32_t vmask = hi_l > lo_l ? (low_mask(hi_l) & ~low_mask(lo_l)) : 0u;
+            vmask_all = vmask;
             uint32_t H = 0;
             bool changed = false;
 #pragma unroll
@@ -431,6 +432,9 @@ k_rows(const RowArgs a) {
             }
         }
         S.lmask[lane] = L;
+        // a window is "plain" when every valid byte is kept or a separator (already-clean text): tokens are then exactly
+        // the gaps between separators and pass B skips the kept-byte analysis
+        const bool plain = __all_sync(0xFFFFFFFFu, (L | SP) == vmask_all);
         // token starts: one after every separator
         const int nsp = __popc(SP);
         int incl = nsp;
@@ -561,13 +565,20 @@ k_rows(const RowArgs a) {
                     s[u] = S.tok[tt];
                     e[u] = (int)S.tok[tt + 1] - 1;
                     const int len = e[u] - s[u];
-                    const uint32_t bits = __funnelshift_r(S.lmask[s[u] >> 5], S.lmask[(s[u] >> 5) + 1], s[u] & 31) & low_mask(min(len, 32));
-                    const int f = __ffs(bits) - 1;  // -1 when no kept byte
-                    n[u] = (uint32_t)__popc(bits);
-                    fast[u] = valid[u] && len <= 32 && bits != 0u && (bits >> (f & 31)) == low_mask((int)n[u]);
-                    empty[u] = valid[u] && len <= 32 && bits == 0u;
-                    slow[u] = valid[u] && !fast[u] && !empty[u];
-                    s[u] = fast[u] ? s[u] + f : s[u];  // fast tokens: s now points at the first kept byte
+                    if (plain) {  // every byte between two separators is kept
+                        n[u] = (uint32_t)len;
+                        fast[u] = valid[u] && len > 0;
+                        empty[u] = valid[u] && len == 0;
+                        slow[u] = false;
+                    } else {
+                        const uint32_t bits = __funnelshift_r(S.lmask[s[u] >> 5], S.lmask[(s[u] >> 5) + 1], s[u] & 31) & low_mask(min(len, 32));
+                        const int f = __ffs(bits) - 1;  // -1 when no kept byte
+                        n[u] = (uint32_t)__popc(bits);
+                        fast[u] = valid[u] && len <= 32 && bits != 0u && (bits >> (f & 31)) == low_mask((int)n[u]);
+                        empty[u] = valid[u] && len <= 32 && bits == 0u;
+                        slow[u] = valid[u] && !fast[u] && !empty[u];
+                        s[u] = fast[u] ? s[u] + f : s[u];  // fast tokens: s now points at the first kept byte
+                    }
                 }
                 // ---- phase 2: murmur3 of a contiguous token, first 12 bytes straight-line
                 int nn[TPL];
