@@ -593,13 +593,15 @@ k_rows(const RowArgs a) {
                     b0[u] = __funnelshift_r(w0, w1, sh8) & low_mask(8 * nn[u]);
                     b1[u] = __funnelshift_r(w1, w2, sh8) & low_mask(8 * max(nn[u] - 4, 0));
                     b2[u] = __funnelshift_r(w2, w3, sh8) & low_mask(8 * max(nn[u] - 8, 0));
+                    // a block past the token is all zero and mm_k(0) = 0, so "h ^= mm_k(block)" covers both the tail block
+                    // and the blocks beyond it: one select per block (full block -> rotate/multiply step)
                     uint32_t hh = 42u;
-                    uint32_t kk = mm_k(b0[u]);
-                    hh = nn[u] >= 4 ? mm_h(hh, kk) : (nn[u] > 0 ? hh ^ kk : hh);
-                    kk = mm_k(b1[u]);
-                    hh = nn[u] >= 8 ? mm_h(hh, kk) : (nn[u] > 4 ? hh ^ kk : hh);
-                    kk = mm_k(b2[u]);
-                    hh = nn[u] >= 12 ? mm_h(hh, kk) : (nn[u] > 8 ? hh ^ kk : hh);
+                    uint32_t t = hh ^ mm_k(b0[u]);
+                    hh = nn[u] >= 4 ? rotl32(t, 13) * 5u + 0xe6546b64u : t;
+                    t = hh ^ mm_k(b1[u]);
+                    hh = nn[u] >= 8 ? rotl32(t, 13) * 5u + 0xe6546b64u : t;
+                    t = hh ^ mm_k(b2[u]);
+                    hh = nn[u] >= 12 ? rotl32(t, 13) * 5u + 0xe6546b64u : t;
                     h[u] = hh;
                     any_long |= nn[u] > 12;
                 }
