@@ -233,6 +233,36 @@ struct HashState {
     }
 };
 
+// SWAR classification of four bytes: bit 7 of each byte of l80 / s80 says "kept letter" / "separator"; nx is the word with
+// its ASCII upper-case letters folded; H collects the high bits (non-ASCII bytes present).
+//   CLEAN : lower() + regexp_replace("[^a-zA-Z ]", "") + split("\\s"): letters are kept, ' ' separates, the rest vanishes
+//   !CLEAN: Tokenizer on already-clean text: \t \n \v \f \r ' ' separate, every other byte is kept
+template <bool CLEAN>
+__device__ __forceinline__ void classify_word(uint32_t x, uint32_t& l80, uint32_t& s80, uint32_t& nx, uint32_t& H) {
+    if (CLEAN) {
+        const uint32_t v7 = (x | 0x20202020u) & 0x7F7F7F7Fu;
+        const uint32_t ge_a = v7 + 0x1F1F1F1Fu;  // bit7 <=> byte >= 0x61
+        const uint32_t gt_z = v7 + 0x05050505u;  // bit7 <=> byte >= 0x7B
+        l80 = ge_a & ~gt_z & ~x & 0x80808080u;
+        const uint32_t z = x ^ 0x20202020u;
+        s80 = ~(((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z) & 0x80808080u;
+        nx = x | (l80 >> 2);
+        H |= x & 0x80808080u;
+    } else {
+        const uint32_t t = x & 0x7F7F7F7Fu;
+        const uint32_t ge9 = t + 0x77777777u;   // >= 0x09
+        const uint32_t geE = t + 0x72727272u;   // >= 0x0E
+        const uint32_t z = x ^ 0x20202020u;
+        const uint32_t sp = ~(((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z) & 0x80808080u;
+        s80 = ((ge9 & ~geE & ~x) | sp) & 0x80808080u;
+        l80 = ~s80 & 0x80808080u;
+        const uint32_t geA = t + 0x3F3F3F3Fu;   // >= 'A'
+        const uint32_t gtZ = t + 0x25252525u;   // >= '['
+        const uint32_t up80 = geA & ~gtZ & ~x & 0x80808080u;
+        nx = x | (up80 >> 2);
+    }
+}
+
 __device__ __forceinline__ bool letter_at(const uint32_t* lmask, int p) { return (lmask[p >> 5] >> (p & 31)) & 1u; }
 
 // token bytes [s, e) filtered by the letter mask == word (same length already checked)
@@ -331,8 +361,8 @@ k_rows(const RowArgs a) {
     long long row_beg = a.offs[row], row_end = a.offs[row + 1];
     long long wbase = row_beg & ~15LL;             // global byte offset of buffer byte 0
     int lo = (int)(row_beg - wbase);               // first valid byte of the window
-    int hi = (int)min((long long)ROW_CH, row_end - wbase);
-    bool last = (row_end - wbase) <= ROW_CH;
+    bool last = (row_end - wbase) <= ROW_WIN;
+    int hi = last ? (int)(row_end - wbase) : ROW_CH;
     int lbmin = lo;                                // lowest buffer offset a UTF-8 look-back may read
     int buf = 0;
     uint32_t phase0 = 0, phase1 = 0;
@@ -351,6 +381,7 @@ k_rows(const RowArgs a) {
     uint32_t row_sp = 0;   // separators seen
     bool row_letter = false;
     bool big = false;      // deferred to the wide-table kernel (or over the limit there)
+    bool ext_dirty = false;  // lmask[32..33] hold the extension of an earlier window
     bool gt_active = false;  // first token of the window continues a token from the previous window
     HashState gt;            // its state (lane 0 only)
     gt.reset();
@@ -382,28 +413,7 @@ k_rows(const RowArgs a) {
             for (int j = 0; j < 8; ++j) {
                 const uint32_t x = w[j];
                 uint32_t l80, s80, nx;
-                if (CLEAN) {
-                    const uint32_t v7 = (x | 0x20202020u) & 0x7F7F7F7Fu;
-                    const uint32_t ge_a = v7 + 0x1F1F1F1Fu;  // bit7 <=> byte >= 0x61
-                    const uint32_t gt_z = v7 + 0x05050505u;  // bit7 <=> byte >= 0x7B
-                    l80 = ge_a & ~gt_z & ~x & 0x80808080u;
-                    const uint32_t z = x ^ 0x20202020u;
-                    s80 = ~(((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z) & 0x80808080u;
-                    nx = x | (l80 >> 2);
-                    H |= x & 0x80808080u;
-                } else {
-                    const uint32_t t = x & 0x7F7F7F7Fu;
-                    const uint32_t ge9 = t + 0x77777777u;   // >= 0x09
-                    const uint32_t geE = t + 0x72727272u;   // >= 0x0E
-                    const uint32_t z = x ^ 0x20202020u;
-                    const uint32_t sp = ~(((z & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | z) & 0x80808080u;
-                    s80 = ((ge9 & ~geE & ~x) | sp) & 0x80808080u;
-                    l80 = ~s80 & 0x80808080u;
-                    const uint32_t geA = t + 0x3F3F3F3Fu;   // >= 'A'
-                    const uint32_t gtZ = t + 0x25252525u;   // >= '['
-                    const uint32_t up80 = geA & ~gtZ & ~x & 0x80808080u;
-                    nx = x | (up80 >> 2);
-                }
+                classify_word<CLEAN>(x, l80, s80, nx, H);
                 L |= movemask4(l80) << (4 * j);
                 SP |= movemask4(s80) << (4 * j);
                 changed |= (nx != x);
@@ -434,7 +444,7 @@ k_rows(const RowArgs a) {
         S.lmask[lane] = L;
         // a window is "plain" when every valid byte is kept or a separator (already-clean text): tokens are then exactly
         // the gaps between separators and pass B skips the kept-byte analysis
-        const bool plain = __all_sync(0xFFFFFFFFu, (L | SP) == vmask_all);
+        bool plain = __all_sync(0xFFFFFFFFu, (L | SP) == vmask_all);
         // token starts: one after every separator
         const int nsp = __popc(SP);
         int incl = nsp;
@@ -443,7 +453,7 @@ k_rows(const RowArgs a) {
             int v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
             if (lane >= d) incl += v;
         }
-        const int win_sp = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        int win_sp = __shfl_sync(0xFFFFFFFFu, incl, 31);
         {
             int base = 1 + incl - nsp;
             uint32_t sp = SP;
@@ -453,13 +463,59 @@ k_rows(const RowArgs a) {
                 S.tok[base++] = (uint16_t)(32 * lane + b + 1);
             }
         }
+        const int my_ll = L ? (32 * lane + 31 - __clz(L)) : -1;
+        int last_letter = __reduce_max_sync(0xFFFFFFFFu, my_ll);
+        if (hi > ROW_CH) {
+            // ---- extension of a dialogue's last window: bytes [ROW_CH, hi), one word per lane on lanes 0..15
+            const int p4 = ROW_CH + 4 * lane;
+            uint32_t l4 = 0, s4 = 0, v4 = 0;
+            if (lane < ROW_EXT / 4) {
+                const uint32_t x = *reinterpret_cast<const uint32_t*>(rb + p4);
+                uint32_t l80, s80, nx, H = 0;
+                classify_word<CLEAN>(x, l80, s80, nx, H);
+                v4 = low_mask(min(max(hi - p4, 0), 4));
+                l4 = movemask4(l80) & v4;
+                s4 = movemask4(s80) & v4;
+                if (nx != x) *reinterpret_cast<uint32_t*>(rb + p4) = nx;
+                if (CLEAN && H) {
+                    for (int j = 0; j < 4; ++j) {
+                        const int p = p4 + j;
+                        if (!((v4 >> j) & 1u)) continue;
+                        const uint8_t c = rb[p];
+                        if (c == 0xB0 && p - 1 >= lbmin && rb[p - 1] == 0xC4) {
+                            rb[p] = 'i';
+                            l4 |= 1u << j;
+                        } else if (c == 0xAA && p - 2 >= lbmin && rb[p - 1] == 0x84 && rb[p - 2] == 0xE2) {
+                            rb[p] = 'k';
+                            l4 |= 1u << j;
+                        }
+                    }
+                }
+            }
+            plain = plain && __all_sync(0xFFFFFFFFu, (l4 | s4) == v4);
+            const int sh = 4 * (lane & 7);
+            const uint32_t L0 = __reduce_or_sync(0xFFFFFFFFu, lane < 8 ? l4 << sh : 0u);
+            const uint32_t L1 = __reduce_or_sync(0xFFFFFFFFu, lane >= 8 ? l4 << sh : 0u);   // lanes >= 16 hold 0
+            const uint32_t S0 = __reduce_or_sync(0xFFFFFFFFu, lane < 8 ? s4 << sh : 0u);
+            const uint32_t S1 = __reduce_or_sync(0xFFFFFFFFu, lane >= 8 ? s4 << sh : 0u);
+            if (lane < 2) S.lmask[32 + lane] = lane ? L1 : L0;
+            // separators of the extension, appended to the list: lane l looks at bits l of both words
+            const int n0 = __popc(S0);
+            if ((S0 >> lane) & 1u) S.tok[1 + win_sp + __popc(S0 & low_mask(lane))] = (uint16_t)(ROW_CH + lane + 1);
+            if ((S1 >> lane) & 1u) S.tok[1 + win_sp + n0 + __popc(S1 & low_mask(lane))] = (uint16_t)(ROW_CH + 32 + lane + 1);
+            win_sp += n0 + __popc(S1);
+            if (L1) last_letter = ROW_CH + 32 + 31 - __clz(L1);
+            else if (L0) last_letter = ROW_CH + 31 - __clz(L0);
+            ext_dirty = true;
+        } else if (ext_dirty) {
+            if (lane < 2) S.lmask[32 + lane] = 0u;
+            ext_dirty = false;
+        }
         const int T = win_sp + 1;
         if (lane == 0) {
             S.tok[0] = (uint16_t)lo;
             S.tok[T] = (uint16_t)(hi + 1);
         }
-        const int my_ll = L ? (32 * lane + 31 - __clz(L)) : -1;
-        const int last_letter = __reduce_max_sync(0xFFFFFFFFu, my_ll);
         __syncwarp();
 
         // ================= choose + prefetch the next window =================
@@ -488,8 +544,8 @@ k_rows(const RowArgs a) {
             n_lo = (int)(n_beg - n_wbase);
             n_lbmin = n_lo;
         }
-        n_hi = (int)min((long long)ROW_CH, n_end - n_wbase);
-        n_last = (n_end - n_wbase) <= ROW_CH;
+        n_last = (n_end - n_wbase) <= ROW_WIN;
+        n_hi = n_last ? (int)(n_end - n_wbase) : ROW_CH;
         const bool n_loaded = have_next && n_hi > 0;
         if (n_loaded && lane == 0) {
             const uint32_t bytes = (uint32_t)((n_hi + 15) & ~15);

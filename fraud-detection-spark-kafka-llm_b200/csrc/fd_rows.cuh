@@ -12,8 +12,11 @@ __host__ __device__ constexpr int row_warps(int tl) { return tl == 8 ? 16 : 8; }
 constexpr long long ROWS_FOR_SMALL_TABLES = 65536;  // batches at least this large may use TL = 8 ...
 constexpr long long MEAN_BYTES_FOR_SMALL_TABLES = 1400;  // ... when their dialogues average at most this many bytes
                                                          // (longer ones would mostly overflow a 256-slot table)
-constexpr int ROW_CH = 1024;                 // bytes per staged window
-constexpr int ROW_RAWBUF = ROW_CH + 16;      // + slack for word over-reads at the end
+constexpr int ROW_CH = 1024;                 // bytes per staged window (32 per lane)
+constexpr int ROW_EXT = 64;                  // a dialogue's LAST window may run this much longer (one word per lane, lanes 0..15):
+                                             // a short remainder is absorbed instead of costing a whole extra window
+constexpr int ROW_WIN = ROW_CH + ROW_EXT;
+constexpr int ROW_RAWBUF = ROW_WIN + 16;     // + slack for word over-reads at the end
 // Dialogues that overflow the shared-memory table are deferred to wide tables in global memory, in two classes
 // by size (a dialogue of b bytes has at most b/2 + 1 tokens, which bounds the table it can need):
 //   medium: table <= 2^MED_LOG2 slots (32 KiB, stays in L2): 8 warps per CTA, MED_CTAS CTAs -> thousands of warps
@@ -34,7 +37,7 @@ template <int TL>
 struct __align__(16) WarpSmem {
     uint8_t raw[2][ROW_RAWBUF];        // TMA-staged windows (double-buffered)
     uint32_t lmask[36];                // letter bitmask of the current window (+ zero tail)
-    uint16_t tok[ROW_CH + 8];          // token start offsets of the current window; epilogue scratch
+    uint16_t tok[ROW_WIN + 8];         // token start offsets of the current window; epilogue scratch
     unsigned long long mbar[2];        // one mbarrier per window buffer
     unsigned long long tab[1 << TL];   // count in the low word, bucket in the high word
 };

@@ -119,6 +119,32 @@ def test_long_rows_windows_wide_table_and_giant_tokens(fd, shipped_model_dir):
     _check_scores(model.transform(rows), ora.transform([t.encode() for t in rows]))
 
 
+def test_last_window_extension_every_length(fd, shipped_model_dir):
+    """A dialogue's last window may run 64 bytes past the 1 KiB window (handled one word per lane): every byte
+    length from just below one window to just past the extension, and around the second window's end, with
+    messy content (punctuation, case, U+0130 / U+212A, runs of separators) and every 16-byte alignment."""
+    model = fd.PipelineModel.load(shipped_model_dir)
+    ora = oracle_for(model)
+    rng = np.random.default_rng(23)
+    pool = " ".join(messy_texts(400, seed=31, max_tokens=30))
+    rows = []
+    for k in list(range(985, 1125)) + list(range(2030, 2150)):
+        o = int(rng.integers(0, len(pool) - k - 1))
+        rows.append(pool[o:o + k])
+        rows.append(("x" * int(rng.integers(1, 40)) + " ") * 60)   # spacer of varying size: shifts the next row's alignment
+        rows[-1] = rows[-1][:int(rng.integers(1, 900))]
+    for k in range(1000, 1100, 3):  # U+0130 / U+212A straddling the window end, spaces and letters in the extension
+        rows.append("a" * k + "İ K b" + " " * (k % 7) + "c")
+        rows.append("Ab " * (k // 3) + "İİKK" + "  zz" * (k % 5))
+    for cleaned in (False, True):
+        rowptr, idx, val = model.featurize(rows, cleaned=cleaned)
+        for t, (ix, vl) in zip(rows, csr_rows(rowptr, idx, val)):
+            src = t.lower().encode() if cleaned else t.encode()
+            eix, evl, _, _ = ora.featurize(src, do_clean=not cleaned)
+            assert ix == eix and vl == evl, f"cleaned={cleaned} len={len(t.encode())} " + repr(t[:20])
+    _check_scores(model.transform(rows), ora.transform([t.encode() for t in rows]))
+
+
 def _tree_model(fd, kind, n_trees, depth, num_features=262144, seed=5):
     synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
     rng = np.random.default_rng(seed)
