@@ -48,8 +48,11 @@ static int upload(fd_handle* h, T** dst, const T* src, size_t n);
 
 // The fused kernels never form the tf-idf value of a split feature: x = count * idf[f] is monotone in the integer
 // count (idf >= 0), so "x <= threshold" is the same as "count <= c*" with c* = the largest count whose PRODUCT, rounded
-// exactly as the device would round it, is still <= threshold.  c* is found here once per (forest, idf) pair and
-// stored in the low word of the node's threshold field.  Any negative or NaN idf entry disables the shortcut.
+// exactly as the device would round it, is still <= threshold.  c* is found here once per (forest, idf) pair.  Any
+// negative or NaN idf entry disables the shortcut.
+// The quantised forest is laid out two levels per 32-byte record (Model::nodes_s): a walk is bound by the L2 -> L1
+// sector traffic of its node fetches (one 32-byte sector per fetch whatever the node size), so a record carries a
+// split node AND both its children and one fetch decides two levels.
 int prepare_fused(fd_handle* h) {
     if (!h->fused_dirty) return FD_OK;
     Model& m = h->m;
@@ -57,8 +60,9 @@ int prepare_fused(fd_handle* h) {
     m.int_walk = 0;
     if (m.classifier != 2 || h->host_nodes.empty()) return FD_OK;
     const bool has_idf = !h->host_idf.empty();
-    std::vector<Node> q = h->host_nodes;
-    for (auto& nd : q) {
+    const std::vector<Node>& q = h->host_nodes;
+    std::vector<int32_t> cs(q.size(), 0);
+    for (const auto& nd : q) {
         if (nd.feat < 0) continue;
         const double w = has_idf ? h->host_idf[(size_t)nd.feat] : 1.0;
         const double thr = nd.thr;
@@ -79,13 +83,37 @@ int prepare_fused(fd_handle* h) {
                 if (c >= 0 && prod > thr) --c; else break;
             }
         }
-        int32_t ci = (int32_t)c;
-        uint64_t bits;
-        memcpy(&bits, &nd.thr, 8);
-        bits = (bits & 0xFFFFFFFF00000000ULL) | (uint32_t)ci;
-        memcpy(&nd.thr, &bits, 8);
+        cs[(size_t)(&nd - q.data())] = (int32_t)c;
     }
-    int rc = upload(h, &m.nodes_q, q.data(), q.size());
+    constexpr uint32_t LEAF = 0x7FFFFFFFu;
+    std::vector<uint32_t> sec(8 * q.size(), 0u);
+    auto is_leaf = [&](int n) { return q[(size_t)n].feat < 0; };
+    for (size_t n = 0; n < q.size(); ++n) {
+        uint32_t* w = &sec[8 * n];
+        if (is_leaf((int)n)) {  // only ever fetched for a tree that is a single leaf: both "children" answer with this node
+            w[0] = 0u;
+            w[5] = 0x7FFFFFFFu;
+            w[1] = w[2] = LEAF;
+            w[3] = w[4] = (uint32_t)n;
+            continue;
+        }
+        w[0] = (uint32_t)q[n].feat;
+        w[5] = (uint32_t)cs[n];
+        for (int side = 0; side < 2; ++side) {
+            const int c = q[n].child + side;
+            if (is_leaf(c)) {
+                w[1 + side] = LEAF;
+                w[3 + side] = (uint32_t)c;
+                w[6 + side] = 0u;
+            } else {
+                const int g = q[(size_t)c].child;
+                w[1 + side] = (uint32_t)q[(size_t)c].feat | (is_leaf(g) ? 0x80000000u : 0u);
+                w[3 + side] = (uint32_t)g | (is_leaf(g + 1) ? 0x80000000u : 0u);
+                w[6 + side] = (uint32_t)cs[(size_t)c];
+            }
+        }
+    }
+    int rc = upload(h, reinterpret_cast<uint32_t**>(&m.nodes_s), sec.data(), sec.size());
     if (rc) return rc;
     m.int_walk = 1;
     return FD_OK;
@@ -142,7 +170,7 @@ int fd_destroy(fd_handle* h) {
     cudaFree(m.idf);
     cudaFree(m.coef);
     cudaFree(m.nodes);
-    cudaFree(m.nodes_q);
+    cudaFree(m.nodes_s);
     cudaFree(m.roots);
     cudaFree(m.leaf2);
     cudaFree(m.leaf_prob);

@@ -75,8 +75,12 @@ struct Model {
     double intercept = 0.0, raw_threshold = 0.0;
     int kind = 0, n_trees = 0, n_classes = 2;
     Node* nodes = nullptr;
-    Node* nodes_q = nullptr;   // same forest with every split threshold pre-quantised to a TERM COUNT (see prepare_fused)
-    int int_walk = 0;          // 1: the fused kernels walk nodes_q with integer compares
+    // same forest for the fused kernels: split thresholds pre-quantised to TERM COUNTS and two levels per 32-byte
+    // record (see prepare_fused): record n = { X.feat, L.feat, R.feat, L.child, R.child, X.c*, L.c*, R.c* } for the
+    // split node n = X and its children L, R.  A child that is a leaf has feat = 0x7FFFFFFF and its own node id in the
+    // child word; bit 31 of L.feat / L.child says that L's left / right child is a leaf (same for R).
+    uint4* nodes_s = nullptr;
+    int int_walk = 0;          // 1: the fused kernels walk nodes_s with integer compares
     int32_t* roots = nullptr;  // absolute root index per tree
     double2* leaf2 = nullptr;  // DT: raw class stats, RF: stats / total (0,0 when total == 0)
     double2* leaf_prob = nullptr;  // DT: stats / total, divided once on the host (IEEE division: same bits as on the device)
@@ -106,7 +110,7 @@ struct fd_handle {
     char* hbuf[3] = {nullptr, nullptr, nullptr};
     size_t hbuf_bytes[3] = {0, 0, 0};
     fd::Ctrl* pinned_ctrl = nullptr;
-    // host copies needed to (re)build nodes_q when the idf vector or the forest changes
+    // host copies needed to (re)build nodes_s when the idf vector or the forest changes
     std::vector<fd::Node> host_nodes;
     std::vector<double> host_idf;
     bool fused_dirty = false;

@@ -921,21 +921,30 @@ __device__ __forceinline__ void write_result(const RowArgs& a, long long row, in
 }
 
 // walk one tree with the dialogue's (bucket -> count) table; returns the absolute leaf index
-__device__ __forceinline__ int walk_tree(const Model& m, const unsigned long long* tab, int log2cap, int root, Node& leaf) {
+// one 32-byte record per lane in ONE load (LDG.256): a divergent fetch costs the L1 one wavefront per lane and
+// instruction, so two 16-byte loads of the same sector would double the cost of the step that bounds forest walks
+__device__ __forceinline__ void ldg_256(const uint4* p, uint4& a, uint4& b) {
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+                 : "l"(p));
+}
+
+// returns the node id of the leaf the dialogue's count table reaches from `root`
+__device__ __forceinline__ int walk_tree(const Model& m, const unsigned long long* tab, int log2cap, int root) {
     int n = root;
     if (m.int_walk) {
-        // thresholds pre-quantised to term counts (prepare_fused): a level is one node load, one table probe, one
-        // integer compare -- no idf load and no fp64 on the dependent chain
+        // two levels per 32-byte record, thresholds pre-quantised to term counts (prepare_fused): a fetch, two table
+        // probes and two integer compares decide two levels -- no idf load and no fp64 on the dependent chain
         for (;;) {
-            const uint4 q = __ldg(reinterpret_cast<const uint4*>(m.nodes_q + n));
-            if ((int)q.z < 0) {
-                leaf.thr = __hiloint2double((int)q.y, (int)q.x);
-                leaf.feat = (int)q.z;
-                leaf.child = (int)q.w;
-                return n;
-            }
-            const int cnt = (int)tab_lookup(tab, log2cap, q.z);
-            n = (int)q.w + ((cnt <= (int)q.x) ? 0 : 1);
+            uint4 q0, q1;
+            ldg_256(m.nodes_s + 2 * (size_t)n, q0, q1);
+            const bool r1 = (int)tab_lookup(tab, log2cap, q0.x) > (int)q1.y;
+            const uint32_t cf = r1 ? q0.z : q0.y, cc = r1 ? q1.x : q0.w;
+            const int ccs = (int)(r1 ? q1.w : q1.z);
+            if ((cf & 0x7FFFFFFFu) == 0x7FFFFFFFu) return (int)cc;  // the child is a leaf
+            const bool r2 = (int)tab_lookup(tab, log2cap, cf & 0x7FFFFFFFu) > ccs;
+            n = (int)(cc & 0x7FFFFFFFu) + (r2 ? 1 : 0);
+            if ((r2 ? cc : cf) >> 31) return n;                     // the grandchild is a leaf
         }
     }
     for (;;) {
@@ -944,10 +953,7 @@ __device__ __forceinline__ int walk_tree(const Model& m, const unsigned long lon
         nd.thr = __hiloint2double((int)q.y, (int)q.x);
         nd.feat = (int)q.z;
         nd.child = (int)q.w;
-        if (nd.feat < 0) {
-            leaf = nd;
-            return n;
-        }
+        if (nd.feat < 0) return n;
         const uint32_t cnt = tab_lookup(tab, log2cap, (uint32_t)nd.feat);
         const double x = cnt ? feat_value(m, (uint32_t)nd.feat, cnt) : 0.0;
         n = nd.child + ((x <= nd.thr) ? 0 : 1);
@@ -1008,8 +1014,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
         const double p0 = 1.0 / (1.0 + exp(mg));
         write_result(a, row, lane, mg > m.raw_threshold ? 1.0 : 0.0, p0, 1.0 - p0, -mg, mg);
     } else if (MODE == MODE_DT) {
-        Node leaf;
-        const int n = walk_tree(m, tab, log2cap, __ldg(m.roots), leaf);
+        const int n = walk_tree(m, tab, log2cap, __ldg(m.roots));
         const double2 st = __ldg(m.leaf2 + n), pr = __ldg(m.leaf_prob + n);
         write_result(a, row, lane, st.y > st.x ? 1.0 : 0.0, pr.x, pr.y, st.x, st.y);
     } else if (MODE == MODE_RF) {
@@ -1017,8 +1022,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
         for (int b = 0; b < m.n_trees; b += 32) {
             const int t = b + lane;
             if (t < m.n_trees) {
-                Node leaf;
-                const int n = walk_tree(m, tab, log2cap, __ldg(m.roots + t), leaf);
+                const int n = walk_tree(m, tab, log2cap, __ldg(m.roots + t));
                 const double2 st = __ldg(m.leaf2 + n);
                 scratch[lane] = st.x;
                 scratch[32 + lane] = st.y;
@@ -1036,9 +1040,8 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
         for (int b = 0; b < m.n_trees; b += 32) {
             const int t = b + lane;
             if (t < m.n_trees) {
-                Node leaf;
-                walk_tree(m, tab, log2cap, __ldg(m.roots + t), leaf);
-                scratch[lane] = __dmul_rn(leaf.thr, __ldg(m.tree_w + t));
+                const int n = walk_tree(m, tab, log2cap, __ldg(m.roots + t));
+                scratch[lane] = __dmul_rn(__ldg(&m.nodes[n].thr), __ldg(m.tree_w + t));
             }
             __syncwarp();
             if (lane == 0) mg = ordered_sum(mg, scratch, min(32, m.n_trees - b));
