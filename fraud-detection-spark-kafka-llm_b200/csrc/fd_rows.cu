@@ -201,6 +201,40 @@ __device__ __forceinline__ uint32_t tab_lookup(const unsigned long long* tab, in
     }
 }
 
+// Forest walks probe the count table ~20 times per tree, mostly for features the dialogue does not have, and a
+// linear-probe loop costs the warp its slowest lane every time.  For forests the epilogue therefore builds a
+// loop-free front: fidx[g(f)] = 1 + table slot of THE present feature that maps to g, 0 when none does (the
+// common case: the feature is absent, no table access at all), FIDX_MANY when several do (probe the table).
+constexpr int FIDX_LOG2 = 10;               // 1,024 16-bit entries = 2 KiB (the token-list area, free in the epilogue)
+constexpr uint32_t FIDX_MANY = 0xFFFFu;
+__device__ __forceinline__ uint32_t fidx_slot(uint32_t f) { return (f * 0x85EBCA6Bu) >> (32 - FIDX_LOG2); }
+
+__device__ __forceinline__ void build_fidx(const unsigned long long* tab, int log2cap, uint16_t* fidx, int lane) {
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = lane; i < (2 << FIDX_LOG2) / 16; i += 32) reinterpret_cast<uint4*>(fidx)[i] = z;
+    __syncwarp();
+    const int cap = 1 << log2cap;
+    for (int i = lane; i < cap; i += 32) {
+        const uint32_t k = (uint32_t)(tab[i] >> 32);
+        if (k != EMPTY_KEY) fidx[fidx_slot(k)] = (uint16_t)(i + 1);
+    }
+    __syncwarp();
+    for (int i = lane; i < cap; i += 32) {  // whoever lost a slot marks it shared
+        const uint32_t k = (uint32_t)(tab[i] >> 32);
+        if (k != EMPTY_KEY && fidx[fidx_slot(k)] != (uint16_t)(i + 1)) fidx[fidx_slot(k)] = (uint16_t)FIDX_MANY;
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ uint32_t tab_lookup(const unsigned long long* tab, int log2cap, const uint16_t* fidx, uint32_t idx) {
+    if (fidx == nullptr) return tab_lookup(tab, log2cap, idx);
+    const uint32_t j = fidx[fidx_slot(idx)];
+    if (j == 0u) return 0u;
+    if (j == FIDX_MANY) return tab_lookup(tab, log2cap, idx);
+    const unsigned long long e = tab[j - 1u];
+    return (uint32_t)(e >> 32) == idx ? (uint32_t)e : 0u;
+}
+
 // resumable murmur3 state for tokens whose kept bytes are not contiguous (or span windows)
 struct HashState {
     uint32_t h, k, n, b0, b1, b2;
@@ -769,7 +803,7 @@ k_rows(const RowArgs a) {
                     }
                 }
             } else {
-                row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), tab, TLOG2, row, (int)D, lane);
+                row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), reinterpret_cast<double*>(rb), BIG == 0, tab, TLOG2, row, (int)D, lane);
             }
             // reset the table and the per-dialogue state
             __syncwarp();
@@ -930,7 +964,7 @@ __device__ __forceinline__ void ldg_256(const uint4* p, uint4& a, uint4& b) {
 }
 
 // returns the node id of the leaf the dialogue's count table reaches from `root`
-__device__ __forceinline__ int walk_tree(const Model& m, const unsigned long long* tab, int log2cap, int root) {
+__device__ __forceinline__ int walk_tree(const Model& m, const unsigned long long* tab, int log2cap, const uint16_t* fidx, int root) {
     int n = root;
     if (m.int_walk) {
         // two levels per 32-byte record, thresholds pre-quantised to term counts (prepare_fused): a fetch, two table
@@ -938,11 +972,11 @@ __device__ __forceinline__ int walk_tree(const Model& m, const unsigned long lon
         for (;;) {
             uint4 q0, q1;
             ldg_256(m.nodes_s + 2 * (size_t)n, q0, q1);
-            const bool r1 = (int)tab_lookup(tab, log2cap, q0.x) > (int)q1.y;
+            const bool r1 = (int)tab_lookup(tab, log2cap, fidx, q0.x) > (int)q1.y;
             const uint32_t cf = r1 ? q0.z : q0.y, cc = r1 ? q1.x : q0.w;
             const int ccs = (int)(r1 ? q1.w : q1.z);
             if ((cf & 0x7FFFFFFFu) == 0x7FFFFFFFu) return (int)cc;  // the child is a leaf
-            const bool r2 = (int)tab_lookup(tab, log2cap, cf & 0x7FFFFFFFu) > ccs;
+            const bool r2 = (int)tab_lookup(tab, log2cap, fidx, cf & 0x7FFFFFFFu) > ccs;
             n = (int)(cc & 0x7FFFFFFFu) + (r2 ? 1 : 0);
             if ((r2 ? cc : cf) >> 31) return n;                     // the grandchild is a leaf
         }
@@ -964,6 +998,7 @@ __device__ __forceinline__ int walk_tree(const Model& m, const unsigned long lon
 // aligned shared memory, read two doubles per load
 __device__ __forceinline__ double ordered_sum(double acc, const double* src, int cnt) {
     int l = 0;
+#pragma unroll 4
     for (; l + 1 < cnt; l += 2) {
         const double2 v = *reinterpret_cast<const double2*>(src + l);
         acc = __dadd_rn(acc, v.x);
@@ -974,9 +1009,15 @@ __device__ __forceinline__ double ordered_sum(double acc, const double* src, int
 }
 
 template <int MODE>
-__device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long long* tab, int log2cap, long long row, int D,
-                             int lane) {
-    const Model& m = a.m;  // scratch: 64 doubles of warp scratch (the token list, free at this point)
+__device__ void row_epilogue(const RowArgs& a, double* scratch, double* scratch2, bool smem_tab, unsigned long long* tab, int log2cap,
+                             long long row, int D, int lane) {
+    const Model& m = a.m;  // scratch: the token-list area (2 KiB+), scratch2: the finished window buffer (1 KiB+); both free here
+    const uint16_t* fidx = nullptr;
+    if ((MODE == MODE_RF || MODE == MODE_GBT) && smem_tab && m.int_walk && m.n_trees >= 8) {
+        build_fidx(tab, log2cap, reinterpret_cast<uint16_t*>(scratch), lane);
+        fidx = reinterpret_cast<const uint16_t*>(scratch);
+        scratch = scratch2;
+    }
     // sorted order of the compacted entries: tab[perm[i]] (register sort) or tab[i] (in-place sort)
     uint16_t* perm_buf = reinterpret_cast<uint16_t*>(scratch) + 512;  // second KiB of the token-list area
     const uint16_t* perm = nullptr;
@@ -1014,7 +1055,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
         const double p0 = 1.0 / (1.0 + exp(mg));
         write_result(a, row, lane, mg > m.raw_threshold ? 1.0 : 0.0, p0, 1.0 - p0, -mg, mg);
     } else if (MODE == MODE_DT) {
-        const int n = walk_tree(m, tab, log2cap, __ldg(m.roots));
+        const int n = walk_tree(m, tab, log2cap, nullptr, __ldg(m.roots));
         const double2 st = __ldg(m.leaf2 + n), pr = __ldg(m.leaf_prob + n);
         write_result(a, row, lane, st.y > st.x ? 1.0 : 0.0, pr.x, pr.y, st.x, st.y);
     } else if (MODE == MODE_RF) {
@@ -1022,7 +1063,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
         for (int b = 0; b < m.n_trees; b += 32) {
             const int t = b + lane;
             if (t < m.n_trees) {
-                const int n = walk_tree(m, tab, log2cap, __ldg(m.roots + t));
+                const int n = walk_tree(m, tab, log2cap, fidx, __ldg(m.roots + t));
                 const double2 st = __ldg(m.leaf2 + n);
                 scratch[lane] = st.x;
                 scratch[32 + lane] = st.y;
@@ -1040,7 +1081,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long lo
         for (int b = 0; b < m.n_trees; b += 32) {
             const int t = b + lane;
             if (t < m.n_trees) {
-                const int n = walk_tree(m, tab, log2cap, __ldg(m.roots + t));
+                const int n = walk_tree(m, tab, log2cap, fidx, __ldg(m.roots + t));
                 scratch[lane] = __dmul_rn(__ldg(&m.nodes[n].thr), __ldg(m.tree_w + t));
             }
             __syncwarp();

@@ -193,6 +193,17 @@ def test_host_buffer_transform_matches_device(fd):
     assert model.handle().launch_count() > 0
 
 
+def test_sharded_transform_equals_whole(fd, shipped_model_dir):
+    """Byte-balanced shards (one per rank in a multi-GPU job; no collective) give the same rows as one call."""
+    model = fd.PipelineModel.load(shipped_model_dir)
+    texts = messy_texts(900, seed=41, max_tokens=200)
+    whole = model.transform(texts)
+    pk = fd.PackedText.from_strings(texts)
+    parts = [model.transform(pk.shard(r, 3)) for r in range(3)]
+    for col in ("prediction", "probability", "rawPrediction"):
+        assert np.array_equal(np.concatenate([p[col].cpu().numpy() for p in parts]), whole[col].cpu().numpy())
+
+
 def test_empty_batch_and_errors(fd, shipped_model_dir):
     model = fd.PipelineModel.load(shipped_model_dir)
     assert model.transform([]).count() == 0

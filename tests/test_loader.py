@@ -121,6 +121,27 @@ def test_pack_strings_layout(fd):
     assert pk.n_rows == 2 and not pk.is_device
 
 
+def test_shard_by_bytes(fd):
+    """Rank blocks are balanced by bytes, cover every dialogue once, and a shard is a 16-byte
+    aligned view with rebased offsets."""
+    rng = np.random.default_rng(3)
+    texts = ["w" * int(k) for k in rng.lognormal(5.0, 1.0, size=400).astype(int)] + ["", "", "x" * 50000]
+    pk = fd.PackedText.from_strings(texts)
+    for world in (1, 2, 3, 8):
+        b = fd.shard_bounds(pk.offs, world)
+        assert len(b) == world and b[0][0] == 0 and b[-1][1] == pk.n_rows
+        assert all(b[k][1] == b[k + 1][0] for k in range(world - 1))
+        got = []
+        for r in range(world):
+            sh = pk.shard(r, world)
+            assert int(sh.offs[0]) < 16 and sh.n_rows == b[r][1] - b[r][0]
+            got += [bytes(sh.data[int(sh.offs[i]):int(sh.offs[i + 1])]).decode() for i in range(sh.n_rows)]
+        assert got == texts
+    sizes = [int(pk.offs[hi] - pk.offs[lo]) for lo, hi in fd.shard_bounds(pk.offs, 4)]
+    assert max(sizes) <= -(-int(pk.offs[-1]) // 4) + max(len(t) for t in texts)  # at most one dialogue past an even share
+    assert fd.shard_bounds(fd.PackedText.from_strings([]).offs, 2) == [(0, 0), (0, 0)]
+
+
 def test_estimator_params(fd):
     rf = fd.RandomForestClassifier(featuresCol="features", labelCol="labels", numTrees=100, maxDepth=5, seed=42, featureSubsetStrategy="auto")
     assert rf.getNumTrees() == 100 and rf.getOrDefault("impurity") == "gini" and rf.getOrDefault("maxBins") == 32
