@@ -183,6 +183,62 @@ def test_tree_models_fused_and_csr_paths(fd, kind, n_trees, depth, tmp_path):
         assert not np.all(exp[0] == exp[0][0]), "degenerate test: all rows got one label"
 
 
+def _forest_with_idf(fd, kind, idf, depths, num_features, feats, seed):
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    rng = np.random.default_rng(seed)
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"), fd.StopWordsRemover(inputCol="words", outputCol="filtered_words"),
+              fd.HashingTF(inputCol="filtered_words", outputCol="raw_features", numFeatures=num_features),
+              fd.IDFModel(idf, inputCol="raw_features", outputCol="features")]
+    trees = [synth.random_tree(rng, d, feats, idf, regression=(kind == "gbt"), full=bool(i % 2)) for i, d in enumerate(depths)]
+    if kind == "rf":
+        cl = fd.RandomForestClassificationModel(trees, num_features)
+    else:
+        cl = fd.GBTClassificationModel(trees, [1.0] + [0.3] * (len(trees) - 1), num_features)
+    return fd.PipelineModel(stages + [cl])
+
+
+@pytest.mark.parametrize("kind", ["rf", "gbt"])
+@pytest.mark.parametrize("weights", ["plain", "zeros", "negative"])
+def test_tree_walk_corner_cases(fd, kind, weights):
+    """Forests of every small shape (a single leaf, depths 1-4, odd and even, ragged) so that each arrangement of the
+    two-level node records occurs (leaf child, leaf grandchild on either side); idf vectors with zero entries
+    (threshold compare is 0 <= thr whatever the count) and with negative entries (the integer walk is switched off
+    and the kernels compare tf-idf values in fp64)."""
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    num_features = 4096
+    corpus = synth.SynthCorpus(n_words=600, seed=5)
+    feats = synth.hash_terms(corpus.words[corpus.n_stop:corpus.n_stop + 150] + [b""], num_features)
+    rng = np.random.default_rng(17)
+    idf = np.log(501.0 / (rng.integers(0, 500, size=num_features) + 1.0))
+    if weights == "zeros":
+        idf[feats[::3]] = 0.0
+    elif weights == "negative":
+        idf[feats[::4]] *= -1.0
+    depths = [0, 1, 2, 3, 4, 1, 2, 3, 4, 5, 0, 2, 4, 3, 1, 6]
+    model = _forest_with_idf(fd, kind, idf, depths, num_features, feats, seed=3)
+    pk, _ = corpus.sample(400, tokens=60, device="cpu", seed=2)
+    data, offs = pk.data.numpy(), pk.offs.numpy()
+    rows = [bytes(data[offs[i]:offs[i + 1]]) for i in range(400)] + ["", " ", "zzz"]
+    exp = oracle_for(model).transform([r if isinstance(r, bytes) else r.encode() for r in rows])
+    _check_scores(model.transform(rows), exp)
+    rowptr, idx, val = model.featurize(rows)
+    _check_scores(model.score(rowptr, idx, val), exp)
+    assert len(np.unique(exp[2][:, 1])) > 3
+
+
+@pytest.mark.parametrize("kind,n_trees,depth", [("rf", 40, 7), ("gbt", 24, 5), ("dt", 1, 6)])
+def test_forests_in_the_large_batch_shape(fd, kind, n_trees, depth):
+    """Batches of at least 65,536 short dialogues run the 256-slot-table shape of the kernel (16 warps per CTA); the
+    other tree tests are small batches and run the 512-slot shape.  Checked against the C port of the oracle."""
+    from oracle import c_oracle
+    model, corpus = _tree_model(fd, kind, n_trees, depth)
+    pk, _ = corpus.sample(66000, tokens=40, device="cpu", seed=13)
+    res = model.transform(pk, cleaned=False)
+    o = oracle_for(model)
+    co = c_oracle.COracle(model._plan.stop.getOrDefault("stopWords"), False, o.num_features, o.binary, o.idf, o.classifier)
+    _check_scores(res, co.transform(pk.data.numpy(), pk.offs.numpy(), True))
+
+
 def test_host_buffer_transform_matches_device(fd):
     model, corpus = _tree_model(fd, "dt", 1, 5)
     pk, _ = corpus.sample(20000, tokens=50, device="cpu", seed=21)
