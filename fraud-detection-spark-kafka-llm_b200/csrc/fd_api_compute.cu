@@ -271,7 +271,7 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
         if (!h->hs[i]) FD_CUDA(h, cudaStreamCreateWithFlags(&h->hs[i], cudaStreamNonBlocking));
     if (!h->pinned_ctrl) FD_CUDA(h, cudaMallocHost((void**)&h->pinned_ctrl, 4 * sizeof(Ctrl)));
 
-    constexpr int64_t CHUNK_BYTES = 24 << 20;
+    constexpr int64_t CHUNK_BYTES = 64 << 20;  // pinned copies reach their full rate (55.5 GB/s here) from about 64 MiB; 24 MiB chunks ran at ~50
     constexpr int64_t CHUNK_ROWS = 1 << 18;
     int64_t r0 = 0;
     int c = 0;
