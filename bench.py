@@ -175,6 +175,7 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL's version banner must not share stdout with the JSON line
         dist.init_process_group("nccl", device_id=dev)
     model, pk, corpus, stats = build_workload(fd, a.rows, a.tokens, dev, 20261106 + rank)
     h = model.handle(local)
@@ -218,13 +219,16 @@ def main():
     value = world * n / (ms_per_step / 1000.0)
 
     # ---- end to end through the host-buffer C-ABI call (pinned host memory in, host memory out)
-    hdata = torch.empty(pk.data.numel(), dtype=torch.uint8, pin_memory=True)
-    hdata.copy_(pk.data)
-    hoffs = torch.empty(pk.offs.numel(), dtype=torch.int64, pin_memory=True)
-    hoffs.copy_(pk.offs)
-    hp = torch.empty(n, dtype=torch.float64, pin_memory=True)
-    hq = torch.empty((n, 2), dtype=torch.float64, pin_memory=True)
-    hr = torch.empty((n, 2), dtype=torch.float64, pin_memory=True)
+    numa = {}
+    with fd.numa_local(local, numa):  # pinned pages on the GPU's own NUMA node (first touch happens inside)
+        hdata = torch.empty(pk.data.numel(), dtype=torch.uint8, pin_memory=True)
+        hdata.copy_(pk.data)
+        hoffs = torch.empty(pk.offs.numel(), dtype=torch.int64, pin_memory=True)
+        hoffs.copy_(pk.offs)
+        hp = torch.zeros(n, dtype=torch.float64, pin_memory=True)
+        hq = torch.zeros((n, 2), dtype=torch.float64, pin_memory=True)
+        hr = torch.zeros((n, 2), dtype=torch.float64, pin_memory=True)
+        torch.cuda.synchronize(dev)
 
     def e2e_step():
         h.call("fd_transform_host", P(hdata), P(hoffs), n, 1, P(hp), P(hq), P(hr))
@@ -269,7 +273,7 @@ def main():
                         "kernel": "k_rows<DT,clean>", "bytes_per_dialogue": bytes_per_row, "peak_source": peak_src,
                         "duration_ms": ms_per_step},
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(stats["text_bytes"] + 8 * (n + 1)),
-                   "d2h_bytes_per_step": int(40 * n), "ms_per_step": 1000.0 * float(te.item())},
+                   "d2h_bytes_per_step": int(40 * n), "ms_per_step": 1000.0 * float(te.item()), "pinned_numa": numa},
            "gpu_launches": int(launches), "clocks": clocks}
 
     # ---- CPU baseline on this box's host cores (bounded sample), rank 0 at N = 1 only

@@ -6,6 +6,7 @@ module at the repository root."""
 from . import spark_format
 from ._lib import FdError, Handle, LIB_PATH, load_library
 from .evaluation import BinaryClassificationEvaluator, MulticlassClassificationEvaluator, confusion_matrix
+from .hostmem import gpu_numa_node, numa_local
 from .packing import PackedText, pack_strings, shard_bounds
 from .pipeline import Pipeline, PipelineModel, Row, TransformResult, predict_and_get_label
 from .serving import MicroBatcher, classify_batch
