@@ -121,3 +121,39 @@ def test_two_rank_training_grows_the_oracle_trees():
         assert p.exitcode == 0
     got = dict(q.get(timeout=5) for _ in range(2))
     assert got[0] == got[1] and any(len(t) > 1 for t in got[0])
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3, 4])
+def test_oracle_stump_gain_agrees_with_sklearn(seed):
+    """The only offline cross-check for the training rules: on small data with few distinct values per
+    feature both Spark's rule set (as restated in the oracle) and sklearn's exact CART consider the same midpoint
+    thresholds and maximise the same Gini gain.  Tie-breaking differs, so the GAIN of the chosen root split is compared,
+    and the threshold too when both pick the same feature."""
+    from sklearn.tree import DecisionTreeClassifier
+
+    rows_idx, rows_val, labels, f = _toy(n=300, f=12, seed=seed)
+    rowptr, idx, val = _csr(rows_idx, rows_val)
+    feat_of = idx.numpy()
+    thresholds = training.find_splits(feat_of, val.numpy(), f, float(len(labels)), 31)
+    bag = np.ones((1, len(labels)), dtype=np.int64)
+    tree = _oracle_forest(rows_idx, rows_val, labels, f, thresholds, bag, lambda t, nid: range(f), 1)[0]
+    dense = np.zeros((len(labels), f))
+    for i, (ix, vl) in enumerate(zip(rows_idx, rows_val)):
+        dense[i, ix] = vl
+    sk = DecisionTreeClassifier(criterion="gini", max_depth=1, random_state=0).fit(dense, labels).tree_
+
+    def gain_of(feature, threshold):
+        left = dense[:, feature] <= threshold
+        def g(y):
+            p = np.bincount(y, minlength=2) / max(1, len(y))
+            return 1.0 - float((p * p).sum())
+        n = len(labels)
+        return g(labels) - left.sum() / n * g(labels[left]) - (~left).sum() / n * g(labels[~left])
+
+    assert tree.feature[0] >= 0 and sk.feature[0] >= 0
+    g_oracle = gain_of(int(tree.feature[0]), float(tree.threshold[0]))
+    g_sklearn = gain_of(int(sk.feature[0]), float(sk.threshold[0]))
+    assert abs(g_oracle - g_sklearn) < 1e-12
+    if int(tree.feature[0]) == int(sk.feature[0]):
+        # same partition of the training rows (sklearn stores the midpoint rounded to float32-representable doubles)
+        assert np.array_equal(dense[:, sk.feature[0]] <= sk.threshold[0], dense[:, tree.feature[0]] <= tree.threshold[0])
