@@ -735,13 +735,13 @@ k_rows(const RowArgs a) {
                 for (int u = 0; u < TPL; ++u) {
                     stop[u] = false;
                     if (m.sw_perfect) {  // one probe: 16-bit slot -> word id, then the record is compared
+                        // straight-line: the record load is unconditional (id 0 reads record 0 and is masked out), only
+                        // the rare words longer than 12 bytes branch
                         const uint32_t id = reinterpret_cast<const uint16_t*>(swt)[(h[u] * m.sw_mul) >> m.sw_shift];
-                        if (valid[u] && !empty[u] && id) {
-                            const uint4 w = sww[id - 1u];
-                            stop[u] = (w.x == n[u]) && (w.y == b0[u] && w.z == b1[u] && w.w == b2[u]);
-                            if ((w.x & 0x7FFFFFFFu) == n[u] && (w.x & 0x80000000u))
-                                stop[u] = long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s[u], e[u]);
-                        }
+                        const uint4 w = sww[id ? id - 1u : 0u];
+                        const bool cand = valid[u] && !empty[u] && id != 0u;
+                        stop[u] = cand && (w.x == n[u]) && (w.y == b0[u] && w.z == b1[u] && w.w == b2[u]);
+                        if (cand && w.x == (n[u] | 0x80000000u)) stop[u] = long_stop_word_equal(m.sw_pool + w.y, rb, S.lmask, s[u], e[u]);
                     } else if (m.sw_cap) {
                         const uint32_t e1 = swt[h[u] & swmask], e2 = swt[(h[u] >> 10) & swmask];
                         const bool m1 = e1 != 0u && ((e1 ^ h[u]) >> 16) == 0u, m2 = e2 != 0u && ((e2 ^ h[u]) >> 16) == 0u;
@@ -766,7 +766,9 @@ k_rows(const RowArgs a) {
                     const bool interior_empty = empty[u] && s[u] <= last_letter;
                     bool ins = valid[u] && (empty[u] ? (interior_empty && !m.drop_empty) : !stop[u]);
                     uint32_t fi = 0u;
-                    if (ins) {
+                    if (MODE != MODE_FIT && !m.vocab_cap) {  // hashing trick: the bucket is a few integer ops, computed for every lane
+                        fi = empty[u] ? m.empty_idx : feature_index(h[u], m);
+                    } else if (ins) {
                         fi = empty[u] ? empty_index<MODE>(a, 1u) : term_index<MODE>(a, h[u], n[u], b0[u], b1[u], b2[u], rb, S.lmask, s[u], e[u]);
                         ins = fi != NOT_IN_VOCAB;
                     }
