@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstring>
 #include <cmath>
+#include <algorithm>
 #include <vector>
 
 #include "fd_rows.cuh"
@@ -58,6 +59,7 @@ int prepare_fused(fd_handle* h) {
     Model& m = h->m;
     h->fused_dirty = false;
     m.int_walk = 0;
+    m.dt_small = 0;
     if (m.classifier != 2 || h->host_nodes.empty()) return FD_OK;
     const bool has_idf = !h->host_idf.empty();
     const std::vector<Node>& q = h->host_nodes;
@@ -116,6 +118,57 @@ int prepare_fused(fd_handle* h) {
     int rc = upload(h, reinterpret_cast<uint32_t**>(&m.nodes_s), sec.data(), sec.size());
     if (rc) return rc;
     m.int_walk = 1;
+    // decision tree: count only the split features (Model::dt_small)
+    m.dt_small = 0;
+    if (m.kind == FD_KIND_DT) {
+        std::vector<uint32_t> feats;
+        for (const auto& nd : q)
+            if (nd.feat >= 0 && std::find(feats.begin(), feats.end(), (uint32_t)nd.feat) == feats.end()) feats.push_back((uint32_t)nd.feat);
+        bool found = false;
+        uint32_t mul = 1u;
+        int lg = 0;
+        if (feats.size() <= 63) {
+            uint64_t x = 0xD1B54A32D192ED03ULL;
+            for (lg = 7; lg <= 9 && !found; ++lg) {
+                std::vector<uint8_t> used((size_t)1 << lg);
+                for (int trial = 0; trial < 200000 && !found; ++trial) {
+                    x ^= x >> 12; x ^= x << 25; x ^= x >> 27;  // xorshift64*
+                    mul = (uint32_t)((x * 0x2545F4914F6CDD1DULL) >> 32) | 1u;
+                    std::fill(used.begin(), used.end(), (uint8_t)0);
+                    found = true;
+                    for (uint32_t f : feats) {
+                        const uint32_t slot = (f * mul) >> (32 - lg);
+                        if (used[slot]) {
+                            found = false;
+                            break;
+                        }
+                        used[slot] = 1;
+                    }
+                }
+                if (found) break;
+            }
+        }
+        if (found) {
+            std::vector<uint32_t> dtab((size_t)1 << lg, 0xFFFFFFFFu);
+            for (uint32_t f : feats) dtab[(f * mul) >> (32 - lg)] = f;
+            std::vector<uint32_t> sec_dt = sec;
+            for (size_t n = 0; n < q.size(); ++n) {
+                uint32_t* w = &sec_dt[8 * n];
+                if (is_leaf((int)n)) continue;  // (a single-leaf tree reads counter 0 and goes left whatever it holds)
+                w[0] = (w[0] * mul) >> (32 - lg);
+                for (int side = 0; side < 2; ++side)
+                    if ((w[1 + side] & 0x7FFFFFFFu) != LEAF)
+                        w[1 + side] = (w[1 + side] & 0x80000000u) | (((w[1 + side] & 0x7FFFFFFFu) * mul) >> (32 - lg));
+            }
+            rc = upload(h, &m.dt_tab, dtab.data(), dtab.size());
+            if (!rc) rc = upload(h, reinterpret_cast<uint32_t**>(&m.nodes_dt), sec_dt.data(), sec_dt.size());
+            if (rc) return rc;
+            m.dt_mul = mul;
+            m.dt_log2 = lg;
+            m.dt_shift = 32 - lg;
+            m.dt_small = 1;
+        }
+    }
     return FD_OK;
 }
 
@@ -171,6 +224,8 @@ int fd_destroy(fd_handle* h) {
     cudaFree(m.coef);
     cudaFree(m.nodes);
     cudaFree(m.nodes_s);
+    cudaFree(m.nodes_dt);
+    cudaFree(m.dt_tab);
     cudaFree(m.roots);
     cudaFree(m.leaf2);
     cudaFree(m.leaf_prob);
@@ -436,6 +491,7 @@ int fd_set_linear(fd_handle* h, const double* coef_dense, int32_t num_features, 
     h->m.classifier = 1;
     h->m.n_classes = 2;
     h->m.int_walk = 0;
+    h->m.dt_small = 0;
     return FD_OK;
 }
 

@@ -81,6 +81,15 @@ struct Model {
     // child word; bit 31 of L.feat / L.child says that L's left / right child is a leaf (same for R).
     uint4* nodes_s = nullptr;
     int int_walk = 0;          // 1: the fused kernels walk nodes_s with integer compares
+    // A decision tree splits on a handful of features (at most 2^depth - 1), and its prediction depends on the counts
+    // of those features only.  When there are at most 63 of them the fused DT kernel keeps just those counts: a perfect
+    // hash (f * dt_mul) >> dt_shift over 2^dt_log2 slots (dt_tab[slot] = the feature, ~0 = none) indexes per-warp
+    // counters, every other term is dropped after one compare, and nodes_dt is nodes_s with slots in place of features.
+    int dt_small = 0;
+    uint32_t dt_mul = 0;
+    int dt_shift = 0, dt_log2 = 0;
+    uint32_t* dt_tab = nullptr;
+    uint4* nodes_dt = nullptr;
     int32_t* roots = nullptr;  // absolute root index per tree
     double2* leaf2 = nullptr;  // DT: raw class stats, RF: stats / total (0,0 when total == 0)
     double2* leaf_prob = nullptr;  // DT: stats / total, divided once on the host (IEEE division: same bits as on the device)

@@ -184,6 +184,19 @@ __device__ __forceinline__ bool tab_insert(unsigned long long* tab, int log2cap,
 
 template <int MODE>
 __device__ __forceinline__ bool count_term(const RowArgs& a, unsigned long long* tab, int log2cap, uint32_t fi, uint32_t inc, bool binary) {
+    if (MODE == MODE_DT && a.m.dt_small) {
+        // only the tree's own split features are counted (Model::dt_small): one compare drops every other term, and
+        // the dialogue never outgrows its table (nothing is "new", so nothing is ever deferred)
+        const uint32_t slot = (fi * a.m.dt_mul) >> a.m.dt_shift;
+        if (__ldg(a.m.dt_tab + slot) == fi) {
+            unsigned int* c = reinterpret_cast<unsigned int*>(tab) + slot;
+            if (binary)
+                *c = 1u;
+            else
+                atomicAdd(c, inc);
+        }
+        return false;
+    }
     const bool isnew = tab_insert(tab, log2cap, fi, inc, binary);
     if (MODE == MODE_FIT && isnew) atomicAdd(&a.fit_info[fi].y, 1u);  // first occurrence in this document
     return isnew;
@@ -380,7 +393,11 @@ k_rows(const RowArgs a) {
         const long long r0 = deferred_row(item);
         TLOG2 = wide_table_log2(a.offs[r0 + 1] - a.offs[r0]);
     }
-    {
+    const bool dts = MODE == MODE_DT && m.dt_small;  // the table is 2^dt_log2 plain counters (see count_term)
+    if (dts) {
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = lane; i < (1 << m.dt_log2) / 4; i += 32) reinterpret_cast<uint4*>(tab)[i] = z;
+    } else {
         uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);  // count = 0, key = EMPTY
         for (int i = lane; i < (1 << TLOG2) / 2; i += 32) reinterpret_cast<uint4*>(tab)[i] = ff;
     }
@@ -810,7 +827,10 @@ k_rows(const RowArgs a) {
             // reset the table and the per-dialogue state
             __syncwarp();
             if (BIG && have_next) TLOG2 = wide_table_log2(n_end - n_beg);
-            {
+            if (dts) {
+                const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+                for (int i = lane; i < (1 << m.dt_log2) / 4; i += 32) reinterpret_cast<uint4*>(tab)[i] = z;
+            } else {
                 uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);  // count = 0, key = EMPTY
                 for (int i = lane; i < (1 << TLOG2) / 2; i += 32) reinterpret_cast<uint4*>(tab)[i] = ff;
             }
@@ -966,19 +986,20 @@ __device__ __forceinline__ void ldg_256(const uint4* p, uint4& a, uint4& b) {
 }
 
 // returns the node id of the leaf the dialogue's count table reaches from `root`
-__device__ __forceinline__ int walk_tree(const Model& m, const unsigned long long* tab, int log2cap, const uint16_t* fidx, int root) {
+__device__ __forceinline__ int walk_tree(const Model& m, const unsigned long long* tab, int log2cap, const uint16_t* fidx, int root,
+                                         const uint32_t* dtc = nullptr) {  // dtc: the small-DT counters (records hold their slots)
     int n = root;
     if (m.int_walk) {
         // two levels per 32-byte record, thresholds pre-quantised to term counts (prepare_fused): a fetch, two table
         // probes and two integer compares decide two levels -- no idf load and no fp64 on the dependent chain
         for (;;) {
             uint4 q0, q1;
-            ldg_256(m.nodes_s + 2 * (size_t)n, q0, q1);
-            const bool r1 = (int)tab_lookup(tab, log2cap, fidx, q0.x) > (int)q1.y;
+            ldg_256((dtc ? m.nodes_dt : m.nodes_s) + 2 * (size_t)n, q0, q1);
+            const bool r1 = (int)(dtc ? dtc[q0.x] : tab_lookup(tab, log2cap, fidx, q0.x)) > (int)q1.y;
             const uint32_t cf = r1 ? q0.z : q0.y, cc = r1 ? q1.x : q0.w;
             const int ccs = (int)(r1 ? q1.w : q1.z);
             if ((cf & 0x7FFFFFFFu) == 0x7FFFFFFFu) return (int)cc;  // the child is a leaf
-            const bool r2 = (int)tab_lookup(tab, log2cap, fidx, cf & 0x7FFFFFFFu) > ccs;
+            const bool r2 = (int)(dtc ? dtc[cf & 0x7FFFFFFFu] : tab_lookup(tab, log2cap, fidx, cf & 0x7FFFFFFFu)) > ccs;
             n = (int)(cc & 0x7FFFFFFFu) + (r2 ? 1 : 0);
             if ((r2 ? cc : cf) >> 31) return n;                     // the grandchild is a leaf
         }
@@ -1057,7 +1078,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, double* scratch2
         const double p0 = 1.0 / (1.0 + exp(mg));
         write_result(a, row, lane, mg > m.raw_threshold ? 1.0 : 0.0, p0, 1.0 - p0, -mg, mg);
     } else if (MODE == MODE_DT) {
-        const int n = walk_tree(m, tab, log2cap, nullptr, __ldg(m.roots));
+        const int n = walk_tree(m, tab, log2cap, nullptr, __ldg(m.roots), m.dt_small ? reinterpret_cast<const uint32_t*>(tab) : nullptr);
         const double2 st = __ldg(m.leaf2 + n), pr = __ldg(m.leaf_prob + n);
         write_result(a, row, lane, st.y > st.x ? 1.0 : 0.0, pr.x, pr.y, st.x, st.y);
     } else if (MODE == MODE_RF) {

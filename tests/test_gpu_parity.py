@@ -164,7 +164,7 @@ def _tree_model(fd, kind, n_trees, depth, num_features=262144, seed=5):
     return fd.PipelineModel(stages + [cl]), corpus
 
 
-@pytest.mark.parametrize("kind,n_trees,depth", [("dt", 1, 5), ("rf", 100, 10), ("rf", 33, 4), ("gbt", 200, 6), ("gbt", 7, 3)])
+@pytest.mark.parametrize("kind,n_trees,depth", [("dt", 1, 5), ("dt", 1, 9), ("rf", 100, 10), ("rf", 33, 4), ("gbt", 200, 6), ("gbt", 7, 3)])
 def test_tree_models_fused_and_csr_paths(fd, kind, n_trees, depth, tmp_path):
     model, corpus = _tree_model(fd, kind, n_trees, depth)
     pk, _ = corpus.sample(300, tokens=120, device="cpu", seed=9)
