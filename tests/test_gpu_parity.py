@@ -183,6 +183,44 @@ def test_tree_models_fused_and_csr_paths(fd, kind, n_trees, depth, tmp_path):
         assert not np.all(exp[0] == exp[0][0]), "degenerate test: all rows got one label"
 
 
+@pytest.mark.parametrize("featuriser", ["hashing", "hashing-binary", "vocabulary"])
+@pytest.mark.parametrize("kind,n_trees,depth", [("dt", 1, 5), ("dt", 1, 8), ("rf", 20, 6)])
+def test_trees_on_long_and_messy_rows(fd, kind, n_trees, depth, featuriser):
+    """Tree models over the window-edge rows (many windows, multi-window tokens, hundreds of distinct buckets) and
+    messy text, with HashingTF (counts and binary) and with a CountVectorizerModel in front.  A depth-5 tree takes
+    the split-feature-counter path of the fused kernel (no dialogue is ever deferred there); depth 8 and the forest
+    take the full count table, where the first long row overflows into the wide-table kernel."""
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    rng = np.random.default_rng(29)
+    rows = _long_rows() + messy_texts(300, seed=12, max_tokens=120)
+    import collections
+    df = collections.Counter(w for r in rows for w in set("".join(c if c.isalpha() or c == " " else "" for c in r.lower()).split(" ")) if w.isascii())
+    stop = set(fd.load_default_stop_words())
+    pick = [w for w, _ in df.most_common() if 0 < len(w) <= 14 and w not in stop][:300]   # most frequent first
+    if featuriser == "vocabulary":
+        vocab = [""] + pick
+        nf = len(vocab)
+        front = fd.CountVectorizerModel(vocab, inputCol="filtered_words", outputCol="raw_features")
+        feats = np.arange(41)
+    else:
+        nf = 1 << 16
+        front = fd.HashingTF(inputCol="filtered_words", outputCol="raw_features", numFeatures=nf, binary=featuriser.endswith("binary"))
+        feats = synth.hash_terms([w.encode() for w in pick[:40]] + [b""], nf)   # trees split on frequent words: both branches taken
+    idf = np.log(301.0 / (rng.integers(0, 300, size=nf) + 1.0))
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"), fd.StopWordsRemover(inputCol="words", outputCol="filtered_words"),
+              front, fd.IDFModel(idf, inputCol="raw_features", outputCol="features")]
+    if kind == "dt":
+        cl = fd.DecisionTreeClassificationModel(synth.random_tree(rng, depth, feats, idf), nf)
+    else:
+        cl = fd.RandomForestClassificationModel([synth.random_tree(rng, depth, feats, idf, full=False) for _ in range(n_trees)], nf)
+    model = fd.PipelineModel(stages + [cl])
+    exp = oracle_for(model).transform([t.encode() for t in rows])
+    _check_scores(model.transform(rows), exp)
+    rowptr, idx, val = model.featurize(rows)
+    _check_scores(model.score(rowptr, idx, val), exp)
+    assert len(np.unique(exp[2][:, 1])) > 1, "degenerate test: every row reached the same leaf"
+
+
 def _forest_with_idf(fd, kind, idf, depths, num_features, feats, seed):
     synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
     rng = np.random.default_rng(seed)
