@@ -7,13 +7,15 @@
 // one is hashed.  Per window:
 //   pass A  each lane classifies 32 bytes with SWAR arithmetic (letter / separator / dropped),
 //           lower-cases in place, and publishes a letter bitmask, a separator bitmask and the list
-//           of token start offsets;
+//           of token start offsets (a dialogue's last window may run 64 bytes longer: one word per lane);
 //   pass B  one token per lane: MurmurHash3_x86_32(seed 42) straight out of shared memory,
-//           stop-word probe (shared-memory table keyed by the same hash), nonNegativeMod, and an
-//           atomicCAS insert into the warp's open-addressed (bucket -> count) table.
+//           stop-word probe (perfect-hash table in shared memory keyed by the same hash, record compared
+//           byte for byte), nonNegativeMod, and an atomicCAS insert into the warp's open-addressed
+//           (bucket -> count) table.
 // At the end of a dialogue the table is either compacted + bitonic-sorted and appended to the CSR
 // staging buffer (featurize), dotted with the logistic coefficients in ascending-bucket order, or
-// probed directly by a lane-per-tree walk over the 16-byte forest nodes (DT / RF / GBT).
+// probed by a lane-per-tree walk over the forest's two-level 32-byte records (DT / RF / GBT; forests first
+// build a loop-free lookup front over the table, a small decision tree counts only its own split features).
 //
 // Semantics restated from Spark 3.5.5; reference call sites:
 // utils/agent_api.py:143-144 (cleaning), fraud_detection_spark.py:50-53 (Tokenizer, StopWordsRemover,
@@ -745,7 +747,7 @@ k_rows(const RowArgs a) {
                         empty[u] = (n[u] == 0u);
                     }
                 }
-                // ---- phase 3: stop-word lookup: two candidate slots of the cuckoo table, 16-bit fingerprint, then
+                // ---- phase 3: stop-word lookup: perfect-hash slot (or two cuckoo slots with 16-bit fingerprints), then
                 //      the word record is compared (no loop; the long-word compare is a rare call)
                 bool stop[TPL];
 #pragma unroll
