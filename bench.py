@@ -83,8 +83,10 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def build_workload(fd, rows, tokens, device, seed):
-    """-> (model, PackedText on device, corpus, stats)"""
+def build_workload(fd, rows, tokens, device, seed, featurizer="gpu"):
+    """-> (model, PackedText on device, corpus, stats).  ``featurizer`` says who counts the document frequencies of the
+    IDF fit and hashes the tree's split terms: "gpu" = this repo's CUDA path, "oracle" = the CPU oracle (the reference
+    arm uses that one, so that nothing of the CUDA library runs anywhere in it; both give the same model, bit for bit)."""
     import importlib
 
     import torch
@@ -95,22 +97,41 @@ def build_workload(fd, rows, tokens, device, seed):
     feat_stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"),
                    fd.StopWordsRemover(inputCol="words", outputCol="filtered_words"),
                    fd.HashingTF(inputCol="filtered_words", outputCol="raw_features", numFeatures=nf)]
-    # IDF fitted on a 65,536-dialogue sample of the same corpus (document frequencies counted on the GPU)
+    # IDF fitted on a 65,536-dialogue sample of the same corpus
     ns = min(rows, 1 << 16)
-    tf_model = fd.PipelineModel(feat_stages)
-    sample = fd.PackedText(pk.data, pk.offs[:ns + 1])
-    rowptr, idx, _ = tf_model.featurize(sample, cleaned=False)
-    df = torch.bincount(idx.long(), minlength=nf).cpu().numpy()
-    nnz_bar = float(rowptr[-1].item()) / ns
+    words = corpus.words[corpus.n_stop:corpus.n_stop + 12] + [b""]
+    if featurizer == "gpu":
+        tf_model = fd.PipelineModel(feat_stages)
+        sample = fd.PackedText(pk.data, pk.offs[:ns + 1])
+        rowptr, idx, _ = tf_model.featurize(sample, cleaned=False)
+        df = torch.bincount(idx.long(), minlength=nf).cpu().numpy()
+        nnz_bar = float(rowptr[-1].item()) / ns
+        top = synth.hash_terms(words, nf)
+        del tf_model
+    else:
+        from oracle import c_oracle
+        from oracle import spark_oracle as so
+        co = c_oracle.COracle(feat_stages[1].getOrDefault("stopWords"), False, nf, False, None, None)
+        offs_np = pk.offs[:ns + 1].cpu().numpy()
+        data_np = pk.data[:int(offs_np[-1]) + 32].cpu().numpy()
+        rp, ix, _ = co.featurize(data_np, offs_np, True)
+        df = np.bincount(ix[:int(rp[-1])], minlength=nf)
+        nnz_bar = float(rp[-1]) / ns
+        top = np.asarray([so.hashing_tf_index(w, nf) for w in words], dtype=np.int64)
     idf_model = fd.IDF(inputCol="raw_features", outputCol="features").fit_from_doc_freq(df, ns)
     rng = np.random.default_rng(seed)
-    top = synth.hash_terms(corpus.words[corpus.n_stop:corpus.n_stop + 12] + [b""], nf)
     tree = synth.random_tree(rng, 5, top, idf_model.idf)
     model = fd.PipelineModel(feat_stages + [idf_model, fd.DecisionTreeClassificationModel(tree, nf)])
     total_bytes = int(pk.offs[-1].item() - pk.offs[0].item())
     stats = {"L_bar": total_bytes / rows, "nnz_bar": nnz_bar, "text_bytes": total_bytes}
-    del tf_model
     return model, pk, corpus, stats
+
+
+def workload_config(n, tokens, stats, parallelism):
+    """The ``config`` object of the JSON line -- the same for both arms."""
+    return {"workload": f"C2: {n} dialogues/GPU x {tokens} tokens, HashingTF 2^18 + IDF + DecisionTree depth 5 predict",
+            "L_bar_bytes": stats["L_bar"], "nnz_bar": stats["nnz_bar"], "parallelism": parallelism,
+            "l2": "inputs (%.2f GB/GPU) larger than L2" % (stats["text_bytes"] / 1e9), "seed": 20261106}
 
 
 def cpu_port(model, data_np, offs_np, threads):
@@ -147,11 +168,9 @@ def main():
         # oracle stands in, all host threads, on a bounded sample of the same workload.  Rank 0 only.
         if rank != 0:
             return
-        dev = "cuda" if torch.cuda.is_available() else "cpu"
+        dev = "cuda" if torch.cuda.is_available() else "cpu"  # torch only generates the synthetic text here
         rows = min(a.rows, a.cpu_rows)
-        model, pk, _, stats = build_workload(fd, rows, a.tokens, dev, 20261106) if dev == "cuda" else (None,) * 4
-        if model is None:
-            raise SystemExit("the reference arm builds its workload with the GPU featurizer (IDF fit); run it on the GPU box")
+        model, pk, _, stats = build_workload(fd, rows, a.tokens, dev, 20261106, featurizer="oracle")
         data_np, offs_np = pk.data.cpu().numpy(), pk.offs.cpu().numpy()
         for _ in range(a.warmup):
             cpu_port(model, data_np, offs_np[:20001], cores)
@@ -160,11 +179,11 @@ def main():
             t.append(cpu_port(model, data_np, offs_np, cores)[1])
         ms = 1000.0 * float(np.mean(t))
         v = rows / (ms / 1000.0)
+        cfg = workload_config(rows, a.tokens, stats, f"rows over {cores} host threads")
+        cfg["note"] = "Spark local[*] unavailable offline (no JVM/pyspark); CPU port of the oracle, oracle/oracle.c"
         print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
                           "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                          "dtype": "u8/f64", "data": "synthetic",
-                          "config": {"workload": f"C2 sample: {rows} dialogues x {a.tokens} tokens, HashingTF 2^18 + IDF + DecisionTree depth 5",
-                                     "note": "Spark local[*] unavailable offline (no JVM/pyspark); CPU port of the oracle, oracle/oracle.c"},
+                          "dtype": "u8/f64", "data": "synthetic", "config": cfg,
                           "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                            "sample": f"{rows} of the workload's dialogues per step"},
                           "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
@@ -266,9 +285,7 @@ def main():
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f64",
            "data": "synthetic",
-           "config": {"workload": f"C2: {n} dialogues/GPU x {a.tokens} tokens, HashingTF 2^18 + IDF + DecisionTree depth 5 predict",
-                      "L_bar_bytes": stats["L_bar"], "nnz_bar": stats["nnz_bar"], "parallelism": f"rows sharded x{world}, no collective",
-                      "l2": "inputs (%.2f GB/GPU) larger than L2" % (stats["text_bytes"] / 1e9), "seed": 20261106},
+           "config": workload_config(n, a.tokens, stats, f"rows sharded x{world}, no collective"),
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                         "kernel": "k_rows<DT,clean>", "bytes_per_dialogue": bytes_per_row, "peak_source": peak_src,
                         "duration_ms": ms_per_step},
