@@ -19,7 +19,38 @@ __device__ __forceinline__ double csr_value(const int32_t* __restrict__ idx, con
     return (lo < n && __ldg(idx + lo) == f) ? __ldg(val + lo) : 0.0;
 }
 
-__device__ __forceinline__ int walk_csr(const Model& m, const int32_t* idx, const double* val, int n, int root, double& leaf_pred) {
+// Forests read ~1,000 features per dialogue, nearly all of them absent from it, and a binary search pays its full
+// depth for every one.  A warp therefore first builds a loop-free front over its dialogue in shared memory:
+// front[g(f)] = 1 + position of THE feature of the row that maps to g, 0 when none does (absent: answered by one
+// 16-bit load), FRONT_MANY when several do (binary search as before).
+constexpr int FRONT_LOG2 = 10;
+constexpr uint32_t FRONT_MANY = 0xFFFFu;
+__device__ __forceinline__ uint32_t front_slot(uint32_t f) { return (f * 0x85EBCA6Bu) >> (32 - FRONT_LOG2); }
+
+__device__ __forceinline__ void build_front(uint16_t* front, const int32_t* __restrict__ idx, int n, int lane) {
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = lane; i < (2 << FRONT_LOG2) / 16; i += 32) reinterpret_cast<uint4*>(front)[i] = z;
+    __syncwarp();
+    const int m = min(n, (int)FRONT_MANY - 1);  // positions beyond 65,533 cannot be encoded: those features ...
+    for (int i = lane; i < m; i += 32) front[front_slot((uint32_t)__ldg(idx + i))] = (uint16_t)(i + 1);
+    __syncwarp();
+    for (int i = lane; i < n; i += 32) {  // ... and every feature that lost its slot mark it shared
+        const uint32_t g = front_slot((uint32_t)__ldg(idx + i));
+        if (i >= m || front[g] != (uint16_t)(i + 1)) front[g] = (uint16_t)FRONT_MANY;
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ double csr_value(const uint16_t* front, const int32_t* __restrict__ idx, const double* __restrict__ val, int n, int f) {
+    if (front == nullptr) return csr_value(idx, val, n, f);
+    const uint32_t j = front[front_slot((uint32_t)f)];
+    if (j == 0u) return 0.0;
+    if (j == FRONT_MANY) return csr_value(idx, val, n, f);
+    return __ldg(idx + (j - 1u)) == f ? __ldg(val + (j - 1u)) : 0.0;
+}
+
+__device__ __forceinline__ int walk_csr(const Model& m, const uint16_t* front, const int32_t* idx, const double* val, int n, int root,
+                                        double& leaf_pred) {
     int nd = root;
     for (;;) {
         const uint4 q = __ldg(reinterpret_cast<const uint4*>(m.nodes + nd));
@@ -29,7 +60,7 @@ __device__ __forceinline__ int walk_csr(const Model& m, const int32_t* idx, cons
             leaf_pred = thr;
             return nd;
         }
-        nd = (int)q.w + ((csr_value(idx, val, n, feat) <= thr) ? 0 : 1);
+        nd = (int)q.w + ((csr_value(front, idx, val, n, feat) <= thr) ? 0 : 1);
     }
 }
 
@@ -38,8 +69,10 @@ __global__ void __launch_bounds__(256) k_score_csr(const int64_t* __restrict__ r
                                                    double* __restrict__ pred, double* __restrict__ prob,
                                                    double* __restrict__ raw) {
     __shared__ double scratch_all[8][64];
+    __shared__ __align__(16) uint16_t front_all[8][1 << FRONT_LOG2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double* scratch = scratch_all[warp];
+    const bool use_front = m.classifier == 2 && m.n_trees >= 8;
     const long long nwarps = (long long)gridDim.x * 8;
     for (long long row = (long long)blockIdx.x * 8 + warp; row < n_rows; row += nwarps) {
         const long long o = rowptr[row];
@@ -47,6 +80,11 @@ __global__ void __launch_bounds__(256) k_score_csr(const int64_t* __restrict__ r
         const int32_t* idx = idx_all + o;
         const double* val = val_all + o;
         double out_pred, p0, p1, r0, r1;
+        const uint16_t* front = nullptr;
+        if (use_front) {
+            build_front(front_all[warp], idx, n, lane);
+            front = front_all[warp];
+        }
         if (m.classifier == 1) {
             double sum = 0.0;
             for (int b = 0; b < n; b += 32) {
@@ -68,7 +106,7 @@ __global__ void __launch_bounds__(256) k_score_csr(const int64_t* __restrict__ r
             out_pred = mg > m.raw_threshold ? 1.0 : 0.0;
         } else if (m.kind == FD_KIND_DT) {
             double lp;
-            const int nd = walk_csr(m, idx, val, n, __ldg(m.roots), lp);
+            const int nd = walk_csr(m, nullptr, idx, val, n, __ldg(m.roots), lp);
             const double2 st = __ldg(m.leaf2 + nd), pr = __ldg(m.leaf_prob + nd);
             r0 = st.x;
             r1 = st.y;
@@ -81,7 +119,7 @@ __global__ void __launch_bounds__(256) k_score_csr(const int64_t* __restrict__ r
                 const int t = b + lane;
                 if (t < m.n_trees) {
                     double lp;
-                    const int nd = walk_csr(m, idx, val, n, __ldg(m.roots + t), lp);
+                    const int nd = walk_csr(m, front, idx, val, n, __ldg(m.roots + t), lp);
                     const double2 st = __ldg(m.leaf2 + nd);
                     scratch[lane] = st.x;
                     scratch[32 + lane] = st.y;
@@ -106,7 +144,7 @@ __global__ void __launch_bounds__(256) k_score_csr(const int64_t* __restrict__ r
                 const int t = b + lane;
                 if (t < m.n_trees) {
                     double lp;
-                    walk_csr(m, idx, val, n, __ldg(m.roots + t), lp);
+                    walk_csr(m, front, idx, val, n, __ldg(m.roots + t), lp);
                     scratch[lane] = __dmul_rn(lp, __ldg(m.tree_w + t));
                 }
                 __syncwarp();
