@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libfdb200.so")
+LIB_PATH = os.environ.get("FDB200_LIB") or os.path.join(_HERE, "csrc", "libfdb200.so")  # FDB200_LIB: another build of the same ABI (A/B timing)
 
 FD_OK, FD_ERR_INVALID, FD_ERR_CAPACITY, FD_ERR_CUDA, FD_ERR_STATE, FD_ERR_LIMIT = 0, -1, -2, -3, -4, -5
 FD_FLAG_CLEAN = 1

@@ -414,7 +414,10 @@ k_rows(const RowArgs a) {
     long long row_beg = a.offs[row], row_end = a.offs[row + 1];
     long long wbase = row_beg & ~15LL;             // global byte offset of buffer byte 0
     int lo = (int)(row_beg - wbase);               // first valid byte of the window
-    bool last = (row_end - wbase) <= ROW_WIN;
+    // the 64-byte extension of a dialogue's last window pays for dialogues of about one window -- the large-batch
+    // shape; the other shapes (long dialogues, micro-batches, wide tables) keep plain 1 KiB windows and leaner code
+    constexpr int WIN = (TL == 8 && BIG == 0) ? ROW_WIN : ROW_CH;
+    bool last = (row_end - wbase) <= WIN;
     int hi = last ? (int)(row_end - wbase) : ROW_CH;
     int lbmin = lo;                                // lowest buffer offset a UTF-8 look-back may read
     int buf = 0;
@@ -518,7 +521,7 @@ k_rows(const RowArgs a) {
         }
         const int my_ll = L ? (32 * lane + 31 - __clz(L)) : -1;
         int last_letter = __reduce_max_sync(0xFFFFFFFFu, my_ll);
-        if (hi > ROW_CH) {
+        if (WIN > ROW_CH && hi > ROW_CH) {
             // ---- extension of a dialogue's last window: bytes [ROW_CH, hi), one word per lane on lanes 0..15
             const int p4 = ROW_CH + 4 * lane;
             uint32_t l4 = 0, s4 = 0, v4 = 0;
@@ -597,7 +600,7 @@ k_rows(const RowArgs a) {
             n_lo = (int)(n_beg - n_wbase);
             n_lbmin = n_lo;
         }
-        n_last = (n_end - n_wbase) <= ROW_WIN;
+        n_last = (n_end - n_wbase) <= WIN;
         n_hi = n_last ? (int)(n_end - n_wbase) : ROW_CH;
         const bool n_loaded = have_next && n_hi > 0;
         if (n_loaded && lane == 0) {
@@ -785,7 +788,7 @@ k_rows(const RowArgs a) {
                     const bool interior_empty = empty[u] && s[u] <= last_letter;
                     bool ins = valid[u] && (empty[u] ? (interior_empty && !m.drop_empty) : !stop[u]);
                     uint32_t fi = 0u;
-                    if (MODE != MODE_FIT && !m.vocab_cap) {  // hashing trick: the bucket is a few integer ops, computed for every lane
+                    if (MODE != MODE_FIT && !m.vocab_cap && m.mod_pow2) {  // hashing trick, power-of-two numFeatures: one AND, computed for every lane
                         fi = empty[u] ? m.empty_idx : feature_index(h[u], m);
                     } else if (ins) {
                         fi = empty[u] ? empty_index<MODE>(a, 1u) : term_index<MODE>(a, h[u], n[u], b0[u], b1[u], b2[u], rb, S.lmask, s[u], e[u]);
