@@ -31,6 +31,69 @@ __global__ void k_bin_csr(const int32_t* __restrict__ idx, const double* __restr
     }
 }
 
+// ---- bagging: Poisson(rate) bootstrap weights + weighted class totals of the root ------------------------
+// One thread draws 16 consecutive rows of one tree (one 16-byte store).  u = top 32 bits of splitmix64(key) with
+// key = seed, tree, row; the draw is the number of CDF thresholds <= u (thresholds precomputed on the host).
+constexpr int BAG_CDF = 16;
+struct BagCdf {
+    uint32_t thr[BAG_CDF];
+};
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+__global__ void __launch_bounds__(256) k_rf_bag_poisson(uint64_t seed, BagCdf cdf, int n_trees, long long n_rows,
+                                                        const uint8_t* __restrict__ label, uint8_t* __restrict__ bagw,
+                                                        unsigned long long* __restrict__ root) {
+    const long long groups = (n_rows + 15) / 16;  // per tree
+    const long long total = groups * n_trees;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < total + (31 - (total + 31) % 32); g += (long long)gridDim.x * blockDim.x) {
+        // (the loop bound is rounded up to whole warps so that the shuffles below always see 32 lanes)
+        const bool live = g < total;
+        const int t = live ? (int)(g / groups) : 0;
+        const long long r0 = live ? (g % groups) * 16 : 0;
+        uint32_t w[4] = {0u, 0u, 0u, 0u};
+        unsigned int c0 = 0, c1 = 0;
+        if (live) {
+            const uint64_t tkey = splitmix64(seed ^ ((uint64_t)t * 0xD6E8FEB86659FD93ULL));
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const long long r = r0 + j;
+                if (r < n_rows) {
+                    const uint32_t u = (uint32_t)(splitmix64(tkey + (uint64_t)r) >> 32);
+                    unsigned int k = 0;
+                    while (k < BAG_CDF && u >= cdf.thr[k]) ++k;
+                    w[j >> 2] |= k << (8 * (j & 3));
+                    if (label[r]) c1 += k; else c0 += k;
+                }
+            }
+            uint8_t* dst = bagw + (long long)t * n_rows + r0;
+            if (r0 + 16 <= n_rows && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+            } else {
+                for (int j = 0; j < 16 && r0 + j < n_rows; ++j) dst[j] = (uint8_t)(w[j >> 2] >> (8 * (j & 3)));
+            }
+        }
+        // lanes of a warp usually share the tree: reduce when they all do, else add individually
+        const int t0 = __shfl_sync(0xFFFFFFFFu, t, 0);
+        if (__all_sync(0xFFFFFFFFu, t == t0 || !live)) {
+            for (int d = 16; d > 0; d >>= 1) {
+                c0 += __shfl_down_sync(0xFFFFFFFFu, c0, d);
+                c1 += __shfl_down_sync(0xFFFFFFFFu, c1, d);
+            }
+            if ((threadIdx.x & 31) == 0) {
+                if (c0) atomicAdd(root + 2 * t0, (unsigned long long)c0);
+                if (c1) atomicAdd(root + 2 * t0 + 1, (unsigned long long)c1);
+            }
+        } else if (live) {
+            if (c0) atomicAdd(root + 2 * t, (unsigned long long)c0);
+            if (c1) atomicAdd(root + 2 * t + 1, (unsigned long long)c1);
+        }
+    }
+}
+
 // ---- binSeqOp: one warp per (item, column segment) ---------------------------------------------------
 // item = (tree, node, feature).  The warp walks its segment of the feature's column, keeps entries whose
 // row is in the node, and adds the row's bag weight to a warp-private shared-memory histogram
@@ -242,6 +305,35 @@ int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowi
     if (g > h->sm_count * 8) g = h->sm_count * 8;
     k_rf_histogram<<<g, 256, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, label_dev, bagw_dev, node_id_dev, n_rows, n_units, unit_item_dev,
                                       unit_seg_dev, seg_len, item_tree_dev, item_node_dev, item_feat_dev, out_hist_dev);
+    h->launches += 1;
+    FD_CUDA(h, cudaGetLastError());
+    return FD_OK;
+}
+
+int fd_rf_bag_poisson(fd_handle* h, uint64_t seed, double rate, int32_t n_trees, int64_t n_rows, const uint8_t* label_dev,
+                      uint8_t* out_bagw_dev, uint64_t* out_root_dev, void* stream) {
+    if (!h) return FD_ERR_INVALID;
+    if (n_trees <= 0 || n_rows < 0 || !(rate > 0.0) || rate > 32.0 || !out_bagw_dev || !out_root_dev || (n_rows > 0 && !label_dev))
+        return set_err(h, FD_ERR_INVALID, "bad fd_rf_bag_poisson arguments (0 < rate <= 32)");
+    FD_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    FD_CUDA(h, cudaMemsetAsync(out_root_dev, 0, (size_t)n_trees * 2 * sizeof(uint64_t), st));
+    if (n_rows == 0) return FD_OK;
+    // thr[k] = P(X <= k) scaled to 2^32 (saturating); the draw is the number of thresholds <= u, so it is capped at 16
+    // for rates where P(X > 16) is not negligible the tail is folded into 16 -- rate <= 32 is accepted, Spark's default is 1
+    BagCdf cdf;
+    double p = std::exp(-rate), c = 0.0;
+    for (int k = 0; k < BAG_CDF; ++k) {
+        c += p;
+        const double scaled = c * 4294967296.0;
+        cdf.thr[k] = scaled >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)scaled;
+        p *= rate / (double)(k + 1);
+    }
+    const long long total = ((n_rows + 15) / 16) * (long long)n_trees;
+    long long g = (total + 255) / 256;
+    if (g > (long long)h->sm_count * 16) g = (long long)h->sm_count * 16;
+    k_rf_bag_poisson<<<(unsigned)g, 256, 0, st>>>(seed, cdf, n_trees, n_rows, label_dev, out_bagw_dev,
+                                                  reinterpret_cast<unsigned long long*>(out_root_dev));
     h->launches += 1;
     FD_CUDA(h, cudaGetLastError());
     return FD_OK;

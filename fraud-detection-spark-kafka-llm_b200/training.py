@@ -290,6 +290,17 @@ class CudaTreeBackend:
         self.h.call("fd_bin_csr", _lib.ptr(idx), _lib.ptr(val), idx.numel(), _lib.ptr(thr_ptr), _lib.ptr(thr), _lib.ptr(out), self._st())
         return out
 
+    def bag_poisson(self, seed: int, rate: float, n_trees: int, label):
+        """-> (bagw u8 [n_trees, n_rows], root i64 [n_trees, 2]): Poisson(rate) bootstrap weights and the weighted class
+        counts of this rank's rows, one kernel (fd_rf_bag_poisson)."""
+        t = self.torch
+        n = label.numel()
+        bagw = t.empty((n_trees, n), dtype=t.uint8, device=self.device)
+        root = t.empty((n_trees, 2), dtype=t.int64, device=self.device)
+        self.h.call("fd_rf_bag_poisson", C.c_uint64(seed & 0xFFFFFFFFFFFFFFFF), C.c_double(rate), int(n_trees), n, _lib.ptr(label),
+                    _lib.ptr(bagw), _lib.ptr(root), self._st())
+        return bagw, root
+
     def histogram(self, csc, label, bagw, node_id, items, units):
         colptr, rowidx, bins = csc
         it_t, it_n, it_f = items
@@ -375,12 +386,15 @@ class ForestTrainer:
         if fraction >= 1.0:
             sel_f, sel_v = idx, val
         else:
-            g = torch.Generator(device="cpu")
+            # Bernoulli(fraction) row sample drawn where the rows live; only the picked rows' entries are gathered
+            g = torch.Generator(device=rowptr.device)
             g.manual_seed(self.seed + 7919 * (rank + 1))
-            pick = (torch.rand(n_local, generator=g) < fraction).to(rowptr.device)
-            counts = rowptr[1:] - rowptr[:-1]
-            mask = torch.repeat_interleave(pick, counts)
-            sel_f, sel_v = idx[mask], val[mask]
+            rows = torch.nonzero(torch.rand(n_local, generator=g, device=rowptr.device) < fraction).flatten()
+            cnt = rowptr[rows + 1] - rowptr[rows]
+            start = torch.repeat_interleave(rowptr[rows], cnt)
+            first = torch.repeat_interleave(torch.cumsum(cnt, 0) - cnt, cnt)
+            pos = start + (torch.arange(int(cnt.sum()), device=rowptr.device) - first)
+            sel_f, sel_v = idx[pos], val[pos]
         if dist is not None and dist.get_world_size() > 1:
             # every rank needs the SAME sample: all-gather the sampled entries (padded to the longest shard)
             ws = dist.get_world_size()
@@ -435,18 +449,25 @@ class ForestTrainer:
         tt = self._tick("bin+csc", tt)
         labels = labels.to(dev).to(torch.uint8).contiguous()
         # ---- bagging
+        root = None
         if bag_weights is None:
             if self.T == 1:
                 bag_weights = torch.ones((1, n_local), dtype=torch.uint8, device=dev)
-            else:
+            elif hasattr(self.b, "bag_poisson"):
+                # BaggedPoint.convertToBaggedRDD: Poisson(subsamplingRate) per (tree, row), drawn on the device
+                bag_weights, root = self.b.bag_poisson((self.seed + 1) * 1000003 + rank, self.rate, self.T, labels)
+                root = root.to(torch.float64)
+            else:  # stand-in backends of the CPU orchestration tests
                 g = torch.Generator(device=dev)
                 g.manual_seed(self.seed + rank + 1)
                 lam = torch.full((self.T, n_local), self.rate, dtype=torch.float32, device=dev)
                 bag_weights = torch.poisson(lam, generator=g).clamp_(max=255).to(torch.uint8)
         bagw = bag_weights.to(dev).to(torch.uint8).contiguous()
         node_id = torch.ones((self.T, n_local), dtype=torch.int32, device=dev)
-        onehot = torch.stack([(labels == 0), (labels == 1)], 1).to(torch.float64)
-        root = bagw.to(torch.float64) @ onehot  # [T, 2]
+        if root is None:
+            lab1 = labels.to(torch.bool)
+            w1 = (bagw * lab1).sum(dim=1, dtype=torch.int64)
+            root = torch.stack([bagw.sum(dim=1, dtype=torch.int64) - w1, w1], 1).to(torch.float64)  # [T, 2]
         if dist is not None:
             dist.all_reduce(root)
         root = root.cpu().numpy()

@@ -167,6 +167,13 @@ int64_t fd_launch_count(fd_handle* h);
  * thr_ptr int32[num_features+1] indexes thr f64[]. */
 int fd_bin_csr(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int64_t nnz,
                const int32_t* thr_ptr_dev, const double* thr_dev, uint8_t* out_bin_dev, void* stream);
+/* BaggedPoint.convertToBaggedRDD (bootstrap = true, reached from RandomForestClassifier, fraud_detection_spark.py:67-74):
+ * out_bagw u8[n_trees, n_rows] = Poisson(rate) draws (clamped to 255) from a counter-based generator keyed by
+ * (seed, tree, row) -- reproducible, independent of the launch shape; not Spark's XORShift stream (bag weights are an
+ * INPUT of the parity contract).  out_root u64[n_trees, 2] (zeroed by the call) receives the weighted class counts
+ * of this rank's rows: sum over rows of bagw[t, row] * [label[row] == c]. */
+int fd_rf_bag_poisson(fd_handle* h, uint64_t seed, double rate, int32_t n_trees, int64_t n_rows, const uint8_t* label_dev,
+                      uint8_t* out_bagw_dev, uint64_t* out_root_dev, void* stream);
 /* binSeqOp over a node group.  An ITEM is (tree, node, feature): item_tree/item_node/item_feat int32[n_items],
  * items of one node contiguous and in the node's feature-subset order.  For every item the kernel walks the
  * feature's COLUMN (CSC over this rank's row shard: colptr int64[num_features+1], rowidx int32[nnz],

@@ -224,3 +224,28 @@ def test_reference_trainer_flow_example(fd, tmp_path):
         assert report[name]["Test"]["confusion_matrix"].sum() > 200
     saved = fd.PipelineModel.load(str(tmp_path / "fraud_detection_model"))
     assert [type(s).__name__ for s in saved.stages] == ["Tokenizer", "StopWordsRemover", "CountVectorizerModel", "IDFModel", "DecisionTreeClassificationModel"]
+
+
+def test_bag_poisson_kernel(fd):
+    """fd_rf_bag_poisson: Poisson(rate) statistics per tree, reproducible for a seed, independent of launch shape (a
+    prefix of the rows gets the same draws), root class totals equal to the weights summed by label."""
+    h = fd.Handle(0)
+    b = training.CudaTreeBackend(h)
+    n, T = 200_003, 7
+    lab = (torch.rand(n, device="cuda") < 0.3).to(torch.uint8)
+    for rate in (1.0, 0.5, 3.0):
+        bagw, root = b.bag_poisson(1234, rate, T, lab)
+        again, _ = b.bag_poisson(1234, rate, T, lab)
+        other, _ = b.bag_poisson(1235, rate, T, lab)
+        assert torch.equal(bagw, again) and not torch.equal(bagw, other)
+        w = bagw.to(torch.float64)
+        assert abs(float(w.mean()) - rate) < 0.02 * max(1.0, rate) and abs(float(w.var()) - rate) < 0.05 * max(1.0, rate)
+        p0 = float((bagw == 0).double().mean())
+        assert abs(p0 - np.exp(-rate)) < 0.01
+        # trees are independent streams
+        assert abs(float(torch.corrcoef(w[:2])[0, 1])) < 0.02
+        w1 = (bagw * lab.bool()).sum(dim=1, dtype=torch.int64)
+        exp_root = torch.stack([bagw.sum(dim=1, dtype=torch.int64) - w1, w1], 1)
+        assert torch.equal(root, exp_root)
+        short, _ = b.bag_poisson(1234, rate, T, lab[:1001])
+        assert torch.equal(short, bagw[:, :1001])
