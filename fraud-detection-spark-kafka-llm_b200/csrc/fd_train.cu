@@ -98,9 +98,10 @@ __global__ void __launch_bounds__(256) k_rf_bag_poisson(uint64_t seed, BagCdf cd
 // item = (tree, node, feature).  The warp walks its segment of the feature's column, keeps entries whose
 // row is in the node, and adds the row's bag weight to a warp-private shared-memory histogram
 // [32 bins][2 classes]; the non-zero cells are then added to the item's global histogram.
-__global__ void __launch_bounds__(256) k_rf_histogram(const int64_t* __restrict__ colptr, const int32_t* __restrict__ rowidx,
-                                                      const uint8_t* __restrict__ bin, const uint8_t* __restrict__ label,
-                                                      const uint8_t* __restrict__ bagw, const int32_t* __restrict__ node_id,
+// Per entry ONE gather: the row's label rides in bit 31 of the column's row index, and the row's node id and
+// bag weight share one word, state[tree, row] = node_id << 8 | bag_weight.
+__global__ void __launch_bounds__(256) k_rf_histogram(const int64_t* __restrict__ colptr, const uint32_t* __restrict__ rowidx,
+                                                      const uint8_t* __restrict__ bin, const uint32_t* __restrict__ state,
                                                       long long n_rows, int n_units, const int32_t* __restrict__ unit_item,
                                                       const int32_t* __restrict__ unit_seg, int seg_len,
                                                       const int32_t* __restrict__ item_tree, const int32_t* __restrict__ item_node,
@@ -114,17 +115,16 @@ __global__ void __launch_bounds__(256) k_rf_histogram(const int64_t* __restrict_
         h[32 + lane] = 0u;
         __syncwarp();
         const int item = unit_item[u];
-        const int t = item_tree[item], node = item_node[item], f = item_feat[item];
+        const int t = item_tree[item], f = item_feat[item];
+        const uint32_t node = (uint32_t)item_node[item];
         const long long c0 = colptr[f] + (long long)unit_seg[u] * seg_len;
         const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
-        const int32_t* nid = node_id + (long long)t * n_rows;
-        const uint8_t* bw = bagw + (long long)t * n_rows;
+        const uint32_t* st = state + (long long)t * n_rows;
         for (long long e = c0 + lane; e < c1; e += 32) {
-            const int r = rowidx[e];
-            if (nid[r] == node) {
-                const unsigned int w = bw[r];
-                if (w) atomicAdd(&h[(int)bin[e] * 2 + (int)label[r]], w);
-            }
+            const uint32_t rl = rowidx[e];
+            const uint32_t s = st[rl & 0x7FFFFFFFu];
+            const uint32_t w = s & 255u;
+            if ((s >> 8) == node && w) atomicAdd(&h[(int)bin[e] * 2 + (int)(rl >> 31)], w);
         }
         __syncwarp();
         unsigned int* g = hist + (size_t)item * (HB * 2);
@@ -234,8 +234,8 @@ __global__ void __launch_bounds__(128) k_rf_best_split(const unsigned int* __res
 
 // ---- move rows to their children ------------------------------------------------------------------------
 // explicit entries of the split feature: one warp per (split node, column segment)
-__global__ void __launch_bounds__(256) k_rf_advance_explicit(const int64_t* __restrict__ colptr, const int32_t* __restrict__ rowidx,
-                                                             const uint8_t* __restrict__ bin, int32_t* __restrict__ node_id,
+__global__ void __launch_bounds__(256) k_rf_advance_explicit(const int64_t* __restrict__ colptr, const uint32_t* __restrict__ rowidx,
+                                                             const uint8_t* __restrict__ bin, uint32_t* __restrict__ state,
                                                              long long n_rows, int n_units, const int32_t* __restrict__ unit_item,
                                                              const int32_t* __restrict__ unit_seg, int seg_len,
                                                              const int32_t* __restrict__ split_tree, const int32_t* __restrict__ split_node,
@@ -244,28 +244,29 @@ __global__ void __launch_bounds__(256) k_rf_advance_explicit(const int64_t* __re
     const int nwarps = gridDim.x * 8;
     for (int u = blockIdx.x * 8 + (threadIdx.x >> 5); u < n_units; u += nwarps) {
         const int s = unit_item[u];
-        const int node = split_node[s], f = split_feat[s], sb = split_bin[s];
-        int32_t* nid = node_id + (long long)split_tree[s] * n_rows;
+        const uint32_t node = (uint32_t)split_node[s];
+        const int f = split_feat[s], sb = split_bin[s];
+        uint32_t* st = state + (long long)split_tree[s] * n_rows;
         const long long c0 = colptr[f] + (long long)unit_seg[u] * seg_len;
         const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
         for (long long e = c0 + lane; e < c1; e += 32) {
-            const int r = rowidx[e];
-            if (nid[r] == node) nid[r] = ((int)bin[e] <= sb) ? 2 * node : 2 * node + 1;
+            const uint32_t r = rowidx[e] & 0x7FFFFFFFu;
+            const uint32_t v = st[r];
+            if ((v >> 8) == node) st[r] = ((((int)bin[e] <= sb) ? 2u * node : 2u * node + 1u) << 8) | (v & 255u);
         }
     }
 }
 
-// rows still sitting in a split node do not have the feature: they follow bin_of_zero (action = child id),
-// rows of nodes that became leaves keep their id (action < 0)
-__global__ void k_rf_advance_default(int32_t* __restrict__ node_id, long long n_rows, int n_trees, int level_base,
+__global__ void k_rf_advance_default(uint32_t* __restrict__ state, long long n_rows, int n_trees, int level_base,
                                      const int32_t* __restrict__ action) {
     const long long total = n_rows * n_trees;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
-        const int n = node_id[k];
+        const uint32_t v = state[k];
+        const int n = (int)(v >> 8);
         if (n >= level_base && n < 2 * level_base) {
             const int a = action[(k / n_rows) * level_base + (n - level_base)];
-            if (a >= 0) node_id[k] = a;
+            if (a >= 0) state[k] = ((uint32_t)a << 8) | (v & 255u);
         }
     }
 }
@@ -290,9 +291,8 @@ int fd_bin_csr(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int6
     return FD_OK;
 }
 
-int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowidx_dev, const uint8_t* bin_dev,
-                    const uint8_t* label_dev, const uint8_t* bagw_dev, const int32_t* node_id_dev, int64_t n_rows,
-                    int32_t n_items, const int32_t* item_tree_dev, const int32_t* item_node_dev, const int32_t* item_feat_dev,
+int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowidx_dev, const uint8_t* bin_dev,
+                    const uint32_t* state_dev, int64_t n_rows, int32_t n_items, const int32_t* item_tree_dev, const int32_t* item_node_dev, const int32_t* item_feat_dev,
                     int32_t n_units, const int32_t* unit_item_dev, const int32_t* unit_seg_dev, int32_t seg_len,
                     uint32_t* out_hist_dev, void* stream) {
     if (!h) return FD_ERR_INVALID;
@@ -303,7 +303,7 @@ int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowi
     if (n_units == 0) return FD_OK;
     int g = (n_units + 7) / 8;
     if (g > h->sm_count * 8) g = h->sm_count * 8;
-    k_rf_histogram<<<g, 256, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, label_dev, bagw_dev, node_id_dev, n_rows, n_units, unit_item_dev,
+    k_rf_histogram<<<g, 256, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, state_dev, n_rows, n_units, unit_item_dev,
                                       unit_seg_dev, seg_len, item_tree_dev, item_node_dev, item_feat_dev, out_hist_dev);
     h->launches += 1;
     FD_CUDA(h, cudaGetLastError());
@@ -357,8 +357,8 @@ int fd_rf_best_split(fd_handle* h, const uint32_t* hist_dev, int32_t n_nodes, co
     return FD_OK;
 }
 
-int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowidx_dev, const uint8_t* bin_dev,
-                  int32_t* node_id_dev, int64_t n_rows, int32_t n_trees, int32_t level_base, int32_t n_split_nodes,
+int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowidx_dev, const uint8_t* bin_dev,
+                  uint32_t* state_dev, int64_t n_rows, int32_t n_trees, int32_t level_base, int32_t n_split_nodes,
                   const int32_t* split_tree_dev, const int32_t* split_node_dev, const int32_t* split_feat_dev,
                   const int32_t* split_bin_dev, int32_t n_units, const int32_t* unit_item_dev, const int32_t* unit_seg_dev,
                   int32_t seg_len, const int32_t* action_dev, void* stream) {
@@ -370,14 +370,14 @@ int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowidx
     if (n_units > 0) {
         int g = (n_units + 7) / 8;
         if (g > h->sm_count * 8) g = h->sm_count * 8;
-        k_rf_advance_explicit<<<g, 256, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, node_id_dev, n_rows, n_units, unit_item_dev, unit_seg_dev,
+        k_rf_advance_explicit<<<g, 256, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, state_dev, n_rows, n_units, unit_item_dev, unit_seg_dev,
                                                  seg_len, split_tree_dev, split_node_dev, split_feat_dev, split_bin_dev);
         h->launches += 1;
     }
     long long total = n_rows * n_trees;
     long long g2 = (total + 255) / 256;
     if (g2 > (long long)h->sm_count * 16) g2 = (long long)h->sm_count * 16;
-    k_rf_advance_default<<<(unsigned)g2, 256, 0, st>>>(node_id_dev, n_rows, n_trees, level_base, action_dev);
+    k_rf_advance_default<<<(unsigned)g2, 256, 0, st>>>(state_dev, n_rows, n_trees, level_base, action_dev);
     h->launches += 1;
     FD_CUDA(h, cudaGetLastError());
     return FD_OK;

@@ -301,15 +301,17 @@ class CudaTreeBackend:
                     _lib.ptr(bagw), _lib.ptr(root), self._st())
         return bagw, root
 
-    def histogram(self, csc, label, bagw, node_id, items, units):
+    def histogram(self, csc, state, items, units):
+        """csc = (colptr i64, rowidx i32 with the row's label in bit 31, bin u8); state i32 [n_trees, n_rows] =
+        node_id << 8 | bag weight."""
         colptr, rowidx, bins = csc
         it_t, it_n, it_f = items
         u_item, u_seg = units
         n_items = it_t.numel()
         hist = self.torch.empty((n_items, 32, 2), dtype=self.torch.int32, device=self.device)
-        self.h.call("fd_rf_histogram", _lib.ptr(colptr), _lib.ptr(rowidx), _lib.ptr(bins), _lib.ptr(label), _lib.ptr(bagw),
-                    _lib.ptr(node_id), node_id.shape[1], n_items, _lib.ptr(it_t), _lib.ptr(it_n), _lib.ptr(it_f), u_item.numel(),
-                    _lib.ptr(u_item), _lib.ptr(u_seg), SEG_LEN, _lib.ptr(hist), self._st())
+        self.h.call("fd_rf_histogram", _lib.ptr(colptr), _lib.ptr(rowidx), _lib.ptr(bins), _lib.ptr(state), state.shape[1], n_items,
+                    _lib.ptr(it_t), _lib.ptr(it_n), _lib.ptr(it_f), u_item.numel(), _lib.ptr(u_item), _lib.ptr(u_seg), SEG_LEN,
+                    _lib.ptr(hist), self._st())
         return hist
 
     def best_split(self, hist, node_item_ptr, item_feat, node_total, n_splits, bin_of_zero, min_instances, min_info_gain):
@@ -325,12 +327,12 @@ class CudaTreeBackend:
                     _lib.ptr(bg), _lib.ptr(left), _lib.ptr(right), self._st())
         return bi, bs, bg, left, right
 
-    def advance(self, csc, node_id, level_base, splits, units, action):
+    def advance(self, csc, state, level_base, splits, units, action):
         colptr, rowidx, bins = csc
         s_t, s_n, s_f, s_b = splits
         u_item, u_seg = units
-        self.h.call("fd_rf_advance", _lib.ptr(colptr), _lib.ptr(rowidx), _lib.ptr(bins), _lib.ptr(node_id), node_id.shape[1],
-                    node_id.shape[0], int(level_base), s_t.numel(), _lib.ptr(s_t), _lib.ptr(s_n), _lib.ptr(s_f), _lib.ptr(s_b),
+        self.h.call("fd_rf_advance", _lib.ptr(colptr), _lib.ptr(rowidx), _lib.ptr(bins), _lib.ptr(state), state.shape[1],
+                    state.shape[0], int(level_base), s_t.numel(), _lib.ptr(s_t), _lib.ptr(s_n), _lib.ptr(s_f), _lib.ptr(s_b),
                     u_item.numel(), _lib.ptr(u_item), _lib.ptr(u_seg), SEG_LEN, _lib.ptr(action), self._st())
 
 
@@ -442,12 +444,17 @@ class ForestTrainer:
         counts = rowptr[1:] - rowptr[:-1]
         row_of = torch.repeat_interleave(torch.arange(n_local, dtype=torch.int32, device=dev), counts)
         order = torch.argsort(idx, stable=True)
-        csc = (torch.zeros(self.F + 1, dtype=torch.int64, device=dev), row_of[order].contiguous(), bins[order].contiguous())
+        labels = labels.to(dev).to(torch.uint8).contiguous()
+        if self.max_depth > 22:
+            raise ValueError("maxDepth > 22 is not supported (node ids share a 32-bit word with the bag weight)")
+        # column entries carry (row | label << 31): the histogram kernel then needs a single gather per entry
+        row_lab = row_of | (labels.to(torch.int32) << 31)[row_of.long()]
+        csc = (torch.zeros(self.F + 1, dtype=torch.int64, device=dev), row_lab[order].contiguous(), bins[order].contiguous())
+        del row_lab
         torch.cumsum(torch.bincount(idx.long(), minlength=self.F), 0, out=csc[0][1:])
         col_len = np.diff(csc[0].cpu().numpy())
         del order, row_of, bins
         tt = self._tick("bin+csc", tt)
-        labels = labels.to(dev).to(torch.uint8).contiguous()
         # ---- bagging
         root = None
         if bag_weights is None:
@@ -463,7 +470,7 @@ class ForestTrainer:
                 lam = torch.full((self.T, n_local), self.rate, dtype=torch.float32, device=dev)
                 bag_weights = torch.poisson(lam, generator=g).clamp_(max=255).to(torch.uint8)
         bagw = bag_weights.to(dev).to(torch.uint8).contiguous()
-        node_id = torch.ones((self.T, n_local), dtype=torch.int32, device=dev)
+        state = bagw.to(torch.int32) | (1 << 8)  # per (tree, row): node_id << 8 | bag weight; every row starts in the root
         if root is None:
             lab1 = labels.to(torch.bool)
             w1 = (bagw * lab1).sum(dim=1, dtype=torch.int64)
@@ -520,7 +527,7 @@ class ForestTrainer:
                     continue
                 units = _units_device(d_col_len, items[2].long())
                 tt = self._tick("units", tt)
-                hist = self.b.histogram(csc, labels, bagw, node_id, items, units)
+                hist = self.b.histogram(csc, state, items, units)
                 tt = self._tick("kernel:histogram", tt)
                 if dist is not None and dist.get_world_size() > 1:
                     dist.all_reduce(hist)  # integer counts: exact, order-independent
@@ -553,7 +560,7 @@ class ForestTrainer:
             action[sp[:, 0], sp[:, 1] - base] = np.where(bin_of_zero[sp[:, 2]] <= sp[:, 3], 2 * sp[:, 1], 2 * sp[:, 1] + 1)
             d_sp = tuple(torch.from_numpy(np.ascontiguousarray(sp[:, c])).to(dev) for c in range(4))
             units = tuple(torch.from_numpy(a).to(dev) for a in _units(col_len, sp[:, 2]))
-            self.b.advance(csc, node_id, base, d_sp, units, torch.from_numpy(action).to(dev))
+            self.b.advance(csc, state, base, d_sp, units, torch.from_numpy(action).to(dev))
             frontier = next_frontier
             tt = self._tick("kernel:advance", tt)
         self.stats = {"phases_s": dict(self._t), "hist_bytes": float(hist_bytes), "allreduce_calls": float(allreduce_calls), "n_total": float(n_total)}

@@ -176,18 +176,18 @@ int fd_rf_bag_poisson(fd_handle* h, uint64_t seed, double rate, int32_t n_trees,
                       uint8_t* out_bagw_dev, uint64_t* out_root_dev, void* stream);
 /* binSeqOp over a node group.  An ITEM is (tree, node, feature): item_tree/item_node/item_feat int32[n_items],
  * items of one node contiguous and in the node's feature-subset order.  For every item the kernel walks the
- * feature's COLUMN (CSC over this rank's row shard: colptr int64[num_features+1], rowidx int32[nnz],
- * bin u8[nnz]) and adds the bag weight of the entries whose row currently sits in the node:
- * hist[item, bin, class] += bagw[tree, row].  label u8[n_rows], bagw u8[n_trees, n_rows],
- * node_id int32[n_trees, n_rows] (heap numbering, root 1).  Long columns are cut into segments of seg_len
- * entries: UNIT u covers segment unit_seg[u] of item unit_item[u]'s column (one warp per unit).
+ * feature's COLUMN (CSC over this rank's row shard: colptr int64[num_features+1], rowidx u32[nnz] = row index
+ * with the row's LABEL in bit 31, bin u8[nnz]) and adds the bag weight of the entries whose row currently sits in
+ * the node: hist[item, bin, label] += weight.  state u32[n_trees, n_rows] = node_id << 8 | bag_weight (heap
+ * numbering, root 1; node ids below 2^24) -- one gather per column entry.  Long columns are cut into segments of
+ * seg_len entries: UNIT u covers segment unit_seg[u] of item unit_item[u]'s column (one warp per unit).
  * out_hist u32[n_items, 32, 2] is zeroed by the call.  Rows WITHOUT the feature are not added here:
  * fd_rf_best_split adds them after the cross-rank sum (NCCL all-reduce of out_hist by the caller). */
-int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowidx_dev, const uint8_t* bin_dev,
-                    const uint8_t* label_dev, const uint8_t* bagw_dev, const int32_t* node_id_dev, int64_t n_rows,
-                    int32_t n_items, const int32_t* item_tree_dev, const int32_t* item_node_dev,
-                    const int32_t* item_feat_dev, int32_t n_units, const int32_t* unit_item_dev,
-                    const int32_t* unit_seg_dev, int32_t seg_len, uint32_t* out_hist_dev, void* stream);
+int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowidx_dev, const uint8_t* bin_dev,
+                    const uint32_t* state_dev, int64_t n_rows, int32_t n_items, const int32_t* item_tree_dev,
+                    const int32_t* item_node_dev, const int32_t* item_feat_dev, int32_t n_units,
+                    const int32_t* unit_item_dev, const int32_t* unit_seg_dev, int32_t seg_len, uint32_t* out_hist_dev,
+                    void* stream);
 /* binsToBestSplit for a node group (histograms already summed over ranks).  node_item_ptr int32[n_nodes+1]
  * delimits each node's items; node_total f64[n_nodes, 2] = class totals of the node; n_splits
  * int32[num_features], bin_of_zero u8[num_features].  The implied zero-valued rows (node_total - explicit)
@@ -199,16 +199,17 @@ int fd_rf_best_split(fd_handle* h, const uint32_t* hist_dev, int32_t n_nodes, co
                      const uint8_t* bin_of_zero_dev, int32_t min_instances, double min_info_gain,
                      int32_t* out_best_item_dev, int32_t* out_best_split_dev, double* out_best_gain_dev,
                      double* out_left_dev, double* out_right_dev, void* stream);
-/* Move rows to their children after a level whose node ids are [level_base, 2*level_base).  For each split
- * node s (split_tree/node/feat/bin int32[n_split_nodes]) rows holding the feature go to 2*node when
- * bin <= split_bin else 2*node+1 (units as in fd_rf_histogram, unit_item indexes the split list); every
- * other row of that level follows action int32[n_trees, level_base]: the child id that bin_of_zero selects,
- * or -1 when its node became a leaf (the row keeps its id). */
-int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const int32_t* rowidx_dev, const uint8_t* bin_dev,
-                  int32_t* node_id_dev, int64_t n_rows, int32_t n_trees, int32_t level_base, int32_t n_split_nodes,
+/* Move rows to their children after a level whose node ids are [level_base, 2*level_base): the node field of
+ * state (see fd_rf_histogram) is rewritten, the bag weight kept.  For each split node s
+ * (split_tree/node/feat/bin int32[n_split_nodes]) rows holding the feature go to 2*node when bin <= split_bin else
+ * 2*node+1 (units as in fd_rf_histogram, unit_item indexes the split list); every other row of that level follows
+ * action int32[n_trees, level_base]: the child id that bin_of_zero selects, or -1 when its node became a leaf (the
+ * row keeps its id). */
+int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowidx_dev, const uint8_t* bin_dev,
+                  uint32_t* state_dev, int64_t n_rows, int32_t n_trees, int32_t level_base, int32_t n_split_nodes,
                   const int32_t* split_tree_dev, const int32_t* split_node_dev, const int32_t* split_feat_dev,
-                  const int32_t* split_bin_dev, int32_t n_units, const int32_t* unit_item_dev,
-                  const int32_t* unit_seg_dev, int32_t seg_len, const int32_t* action_dev, void* stream);
+                  const int32_t* split_bin_dev, int32_t n_units, const int32_t* unit_item_dev, const int32_t* unit_seg_dev,
+                  int32_t seg_len, const int32_t* action_dev, void* stream);
 
 #ifdef __cplusplus
 }

@@ -17,16 +17,16 @@ class NumpyTreeBackend:
             out[k] = so.bin_value(th[tp[f]:tp[f + 1]], float(v))
         return torch.from_numpy(out)
 
-    def histogram(self, csc, label, bagw, node_id, items, units):
+    def histogram(self, csc, state, items, units):
         colptr, rowidx, bins = (x.numpy() for x in csc)
-        lab, bw, nid = label.numpy(), bagw.numpy(), node_id.numpy()
+        st = state.numpy()
         it_t, it_n, it_f = (x.numpy() for x in items)
         hist = np.zeros((it_t.size, 32, 2), dtype=np.int32)
         for i, (t, n, f) in enumerate(zip(it_t, it_n, it_f)):
             for e in range(colptr[f], colptr[f + 1]):
-                r = rowidx[e]
-                if nid[t, r] == n:
-                    hist[i, bins[e], lab[r]] += int(bw[t, r])
+                r, lab = int(rowidx[e]) & 0x7FFFFFFF, (int(rowidx[e]) >> 31) & 1
+                if st[t, r] >> 8 == n:
+                    hist[i, bins[e], lab] += int(st[t, r] & 255)
         return torch.from_numpy(hist)
 
     def best_split(self, hist, node_item_ptr, item_feat, node_total, n_splits, bin_of_zero, min_instances, min_info_gain):
@@ -50,18 +50,18 @@ class NumpyTreeBackend:
                 bi[j], bs[j], bg[j], left[j], right[j] = a + jj, s, gain, lc, rc
         return tuple(torch.from_numpy(x) for x in (bi, bs, bg, left, right))
 
-    def advance(self, csc, node_id, level_base, splits, units, action):
+    def advance(self, csc, state, level_base, splits, units, action):
         colptr, rowidx, bins = (x.numpy() for x in csc)
-        nid = node_id.numpy()
+        st = state.numpy()
         act = action.numpy()
         for t, n, f, sb in zip(*(x.numpy() for x in splits)):
             for e in range(colptr[f], colptr[f + 1]):
-                r = rowidx[e]
-                if nid[t, r] == n:
-                    nid[t, r] = 2 * n if bins[e] <= sb else 2 * n + 1
-        T, N = nid.shape
+                r = int(rowidx[e]) & 0x7FFFFFFF
+                if st[t, r] >> 8 == n:
+                    st[t, r] = ((2 * n if bins[e] <= sb else 2 * n + 1) << 8) | (st[t, r] & 255)
+        T, N = st.shape
         for t in range(T):
             for r in range(N):
-                n = nid[t, r]
+                n = st[t, r] >> 8
                 if level_base <= n < 2 * level_base and act[t, n - level_base] >= 0:
-                    nid[t, r] = act[t, n - level_base]
+                    st[t, r] = (act[t, n - level_base] << 8) | (st[t, r] & 255)
