@@ -396,6 +396,7 @@ k_rows(const RowArgs a) {
         TLOG2 = wide_table_log2(a.offs[r0 + 1] - a.offs[r0]);
     }
     const bool dts = MODE == MODE_DT && m.dt_small;  // the table is 2^dt_log2 plain counters (see count_term)
+    const bool dts_fast = dts && m.mod_pow2 && !m.vocab_cap;  // ... and buckets are h & (numFeatures - 1)
     if (dts) {
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
         for (int i = lane; i < (1 << m.dt_log2) / 4; i += 32) reinterpret_cast<uint4*>(tab)[i] = z;
@@ -787,6 +788,21 @@ k_rows(const RowArgs a) {
                 for (int u = 0; u < TPL; ++u) {
                     const bool interior_empty = empty[u] && s[u] <= last_letter;
                     bool ins = valid[u] && (empty[u] ? (interior_empty && !m.drop_empty) : !stop[u]);
+                    if (MODE == MODE_DT && dts_fast) {
+                        // small decision tree, power-of-two HashingTF: bucket -> counter slot -> one compare -> one atomic;
+                        // nothing is ever "new", so there is no distinct count to maintain
+                        const uint32_t fi = empty[u] ? m.empty_idx : (h[u] & (uint32_t)(m.num_features - 1));
+                        const uint32_t slot = (fi * m.dt_mul) >> m.dt_shift;
+                        if (ins && __ldg(m.dt_tab + slot) == fi) {
+                            unsigned int* c = reinterpret_cast<unsigned int*>(tab) + slot;
+                            if (binary)
+                                *c = 1u;
+                            else
+                                atomicAdd(c, 1u);
+                        }
+                        pend += __popc(__ballot_sync(0xFFFFFFFFu, empty[u] && !interior_empty));
+                        continue;
+                    }
                     uint32_t fi = 0u;
                     if (MODE != MODE_FIT && !m.vocab_cap && m.mod_pow2) {  // hashing trick, power-of-two numFeatures: one AND, computed for every lane
                         fi = empty[u] ? m.empty_idx : feature_index(h[u], m);
