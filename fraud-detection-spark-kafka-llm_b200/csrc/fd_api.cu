@@ -222,6 +222,7 @@ int fd_destroy(fd_handle* h) {
     cudaFree(m.vocab_pool);
     cudaFree(m.idf);
     cudaFree(m.coef);
+    cudaFree(m.lr_nz);
     cudaFree(m.nodes);
     cudaFree(m.nodes_s);
     cudaFree(m.nodes_dt);
@@ -485,6 +486,19 @@ int fd_set_linear(fd_handle* h, const double* coef_dense, int32_t num_features, 
     FD_CUDA(h, cudaSetDevice(h->device));
     int rc = upload(h, &h->m.coef, coef_dense, (size_t)num_features);
     if (rc) return rc;
+    {
+        std::vector<uint32_t> nz(((size_t)num_features + 31) / 32, 0u);
+        size_t kept = 0;
+        for (int32_t i = 0; i < num_features; ++i)
+            if (coef_dense[i] != 0.0) {  // (NaN counts as non-zero and is kept)
+                nz[(size_t)i >> 5] |= 1u << (i & 31);
+                ++kept;
+            }
+        rc = upload(h, &h->m.lr_nz, nz.data(), nz.size());
+        if (rc) return rc;
+        h->m.lr_keep = (float)kept / (float)num_features;
+        h->m.lr_sparse = kept * 10 <= (size_t)num_features * 9;  // worth a bitmap probe per term from 10 % zeros
+    }
     h->m.intercept = intercept;
     // LogisticRegressionModel.raw2prediction: rawThreshold = log(t / (1 - t)), -inf at 0, +inf at 1
     h->m.raw_threshold = threshold <= 0.0 ? -INFINITY : (threshold >= 1.0 ? INFINITY : std::log(threshold / (1.0 - threshold)));

@@ -72,6 +72,12 @@ struct Model {
     // classifier
     int classifier = 0;  // 0 none, 1 linear, 2 forest
     double* coef = nullptr;
+    // LogisticRegression with exact-zero coefficients (L1 / elastic-net fits; 59 % of the shipped model's): a term whose
+    // coefficient is +-0.0 adds +-0.0 to the margin, which never changes a sum that starts at +0.0, so the fused kernel
+    // drops such terms before they reach the count table (bit i of lr_nz = coef[i] != 0).  lr_keep = fraction kept.
+    uint32_t* lr_nz = nullptr;
+    int lr_sparse = 0;
+    float lr_keep = 1.0f;
     double intercept = 0.0, raw_threshold = 0.0;
     int kind = 0, n_trees = 0, n_classes = 2;
     Node* nodes = nullptr;

@@ -199,6 +199,7 @@ __device__ __forceinline__ bool count_term(const RowArgs& a, unsigned long long*
         }
         return false;
     }
+    if (MODE == MODE_LINEAR && a.m.lr_sparse && !((__ldg(a.m.lr_nz + (fi >> 5)) >> (fi & 31)) & 1u)) return false;  // zero coefficient
     const bool isnew = tab_insert(tab, log2cap, fi, inc, binary);
     if (MODE == MODE_FIT && isnew) atomicAdd(&a.fit_info[fi].y, 1u);  // first occurrence in this document
     return isnew;
@@ -1221,9 +1222,10 @@ __global__ void k_gather_csr(const unsigned long long* __restrict__ tmp, const l
 // launchers
 // ------------------------------------------------------------------------------------------------
 // large batches: pick the kernel shape from the mean dialogue length, on the device (no host synchronisation)
-__global__ void k_pick_shape(const int64_t* __restrict__ offs, long long n_rows, Ctrl* ctrl) {
+// (keep: the fraction of a dialogue's terms that reach the count table -- below 1 for a sparse LogisticRegression)
+__global__ void k_pick_shape(const int64_t* __restrict__ offs, long long n_rows, float keep, Ctrl* ctrl) {
     const long long mean = (offs[n_rows] - offs[0]) / (n_rows > 0 ? n_rows : 1);
-    ctrl->shape = mean <= MEAN_BYTES_FOR_SMALL_TABLES ? 8 : 9;
+    ctrl->shape = (float)mean * keep <= (float)MEAN_BYTES_FOR_SMALL_TABLES ? 8 : 9;
 }
 
 template <int MODE, bool CLEAN, int TL>
@@ -1268,7 +1270,7 @@ static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a0, int med_
     cudaError_t e;
     if (a.n_rows >= ROWS_FOR_SMALL_TABLES) {
         a.pick_shape = 1;
-        k_pick_shape<<<1, 1, 0, st>>>(a.offs, a.n_rows, a.ctrl);
+        k_pick_shape<<<1, 1, 0, st>>>(a.offs, a.n_rows, (MODE == MODE_LINEAR && a.m.lr_sparse) ? a.m.lr_keep : 1.0f, a.ctrl);
         h->launches += 1;
         e = launch_main<MODE, CLEAN, 8>(h, a, st);
         if (e != cudaSuccess) return e;

@@ -277,6 +277,34 @@ def test_forests_in_the_large_batch_shape(fd, kind, n_trees, depth):
     _check_scores(res, co.transform(pk.data.numpy(), pk.offs.numpy(), True))
 
 
+@pytest.mark.parametrize("num_features", [4096, 10000])
+def test_sparse_lr_coefficients_bit_exact(fd, num_features):
+    """LogisticRegression whose coefficient vector is mostly exact zeros (+0.0 and -0.0): the fused kernel drops those
+    terms before counting them, which must not move a single bit of the margin -- also with zero idf entries (products
+    of -0.0), rows whose terms all have zero coefficients (margin = intercept) and empty rows.  A dense vector (no
+    filter) and the CSR scoring path are checked alongside."""
+    rng = np.random.default_rng(num_features)
+    idf = rng.random(num_features) * 3.0
+    idf[rng.integers(0, num_features, size=num_features // 8)] = 0.0
+    texts = messy_texts(600, seed=77, max_tokens=90) + ["", "   ", "zzzz qqqq", "the of and"]
+    for density in (0.05, 0.4, 1.0):
+        coef = rng.normal(0, 1, num_features)
+        zero = rng.random(num_features) >= density
+        coef[zero] = 0.0
+        coef[zero & (rng.random(num_features) < 0.5)] = -0.0
+        stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"), fd.StopWordsRemover(inputCol="words", outputCol="filtered"),
+                  fd.HashingTF(inputCol="filtered", outputCol="raw_features", numFeatures=num_features),
+                  fd.IDFModel(idf, inputCol="raw_features", outputCol="features"),
+                  fd.LogisticRegressionModel(coef, 0.25, featuresCol="features")]
+        model = fd.PipelineModel(stages)
+        exp = oracle_for(model).transform([t.encode() for t in texts])
+        _check_scores(model.transform(texts), exp)
+        rowptr, idx, val = model.featurize(texts)
+        _check_scores(model.score(rowptr, idx, val), exp)
+        if density < 1.0:
+            assert (exp[2][:, 1] == 0.25).sum() >= 3   # rows with no surviving non-zero term sit exactly at the intercept
+
+
 def test_host_buffer_transform_matches_device(fd):
     model, corpus = _tree_model(fd, "dt", 1, 5)
     pk, _ = corpus.sample(20000, tokens=50, device="cpu", seed=21)
