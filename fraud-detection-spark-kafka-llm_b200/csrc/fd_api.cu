@@ -223,6 +223,7 @@ int fd_destroy(fd_handle* h) {
     cudaFree(m.idf);
     cudaFree(m.coef);
     cudaFree(m.lr_nz);
+    cudaFree(m.used_nz);
     cudaFree(m.nodes);
     cudaFree(m.nodes_s);
     cudaFree(m.nodes_dt);
@@ -382,6 +383,8 @@ int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary) {
     Model& m = h->m;
     m.num_features = num_features;
     m.binary = binary ? 1 : 0;
+    m.used_on = 0;    // bitmaps sized for another feature space are not consulted (set the classifier after the featuriser)
+    m.lr_sparse = 0;
     m.mod_pow2 = (num_features & (num_features - 1)) == 0;
     m.mod_magic = m.mod_pow2 ? 0u : (uint32_t)((1ULL << 32) / (uint64_t)num_features);
     m.mod_r32 = (uint32_t)((1ULL << 32) % (uint64_t)num_features);
@@ -574,6 +577,18 @@ int fd_set_forest(fd_handle* h, int32_t kind, int32_t n_trees, const int32_t* tr
     if (!rc) rc = upload(h, &m.roots, roots.data(), roots.size());
     if (!rc && kind == FD_KIND_GBT) rc = upload(h, &m.tree_w, tree_weights, (size_t)n_trees);
     if (rc) return rc;
+    {
+        std::vector<uint32_t> used(((size_t)std::max(h->m.num_features, 1) + 31) / 32, 0u);
+        size_t n_used = 0;
+        for (const auto& nd : nodes)
+            if (nd.feat >= 0 && (size_t)nd.feat / 32 < used.size() && !((used[(size_t)nd.feat >> 5] >> (nd.feat & 31)) & 1u)) {
+                used[(size_t)nd.feat >> 5] |= 1u << (nd.feat & 31);
+                ++n_used;
+            }
+        rc = upload(h, &m.used_nz, used.data(), used.size());
+        if (rc) return rc;
+        m.used_on = h->m.num_features > 0 && n_used * 2 <= (size_t)h->m.num_features;
+    }
     h->host_nodes = nodes;
     h->fused_dirty = true;
     m.kind = kind;

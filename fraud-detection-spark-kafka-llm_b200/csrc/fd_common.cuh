@@ -78,6 +78,10 @@ struct Model {
     uint32_t* lr_nz = nullptr;
     int lr_sparse = 0;
     float lr_keep = 1.0f;
+    // Forests likewise only ever look at the features their nodes split on: bit i of used_nz = some node splits on
+    // feature i; every other term is dropped before the count table (fewer inserts, fewer overflowing dialogues).
+    uint32_t* used_nz = nullptr;
+    int used_on = 0;
     double intercept = 0.0, raw_threshold = 0.0;
     int kind = 0, n_trees = 0, n_classes = 2;
     Node* nodes = nullptr;

@@ -200,6 +200,11 @@ __device__ __forceinline__ bool count_term(const RowArgs& a, unsigned long long*
         return false;
     }
     if (MODE == MODE_LINEAR && a.m.lr_sparse && !((__ldg(a.m.lr_nz + (fi >> 5)) >> (fi & 31)) & 1u)) return false;  // zero coefficient
+    // (not in the 256-slot shape: large batches of short dialogues rarely outgrow their table, and there the bitmap probe
+    // was measured to cost more than the inserts it saves; it pays where dialogues are long -- micro-batches, wide tables)
+    if ((MODE == MODE_DT || MODE == MODE_RF || MODE == MODE_GBT) && a.m.used_on && log2cap != 8 &&
+        !((__ldg(a.m.used_nz + (fi >> 5)) >> (fi & 31)) & 1u))
+        return false;  // no node of the forest splits on this feature
     const bool isnew = tab_insert(tab, log2cap, fi, inc, binary);
     if (MODE == MODE_FIT && isnew) atomicAdd(&a.fit_info[fi].y, 1u);  // first occurrence in this document
     return isnew;
