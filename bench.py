@@ -288,11 +288,23 @@ def main():
     bytes_per_row = stats["L_bar"] + 8.0 + 40.0  # text + offset + three result columns (fused)
     achieved = n * bytes_per_row / (ms_per_step / 1000.0) / 1e9
     traffic = None
+    issue = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         with open(tp) as f:
-            per_dialogue = json.load(f).get("k_rows_dt_clean_bytes_per_dialogue")
-            traffic = None if per_dialogue is None else per_dialogue * n  # DRAM bytes of one launch over this batch
+            cap = json.load(f)
+        per_dialogue = cap.get("k_rows_dt_clean_bytes_per_dialogue")
+        traffic = None if per_dialogue is None else per_dialogue * n  # DRAM bytes of one launch over this batch
+        ipd = cap.get("k_rows_dt_clean_warp_instructions_per_dialogue")
+        if ipd is not None and clocks.get("sm_mhz"):
+            # what actually bounds the kernel: warp-instruction issue (148 SMs x 4 schedulers x 1 instruction per clock);
+            # instructions per dialogue come from the committed ncu capture, the rate from this run
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            peak_issue = sms * 4 * clocks["sm_mhz"] * 1e6
+            ach_issue = ipd * n / (ms_per_step / 1000.0)
+            issue = {"bound": "warp-instruction issue", "warp_instructions_per_dialogue": ipd, "achieved": ach_issue / 1e9,
+                     "peak": peak_issue / 1e9, "unit": "G warp-instr/s", "frac": ach_issue / peak_issue,
+                     "source": "instructions per dialogue from the ncu capture in profiles/traffic.json"}
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f64",
            "data": "synthetic",
@@ -302,7 +314,7 @@ def main():
                         "duration_ms": ms_per_step},
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(stats["text_bytes"] + 8 * (n + 1)),
                    "d2h_bytes_per_step": int(40 * n), "ms_per_step": 1000.0 * float(te.item()), "pinned_numa": numa},
-           "gpu_launches": int(launches), "clocks": clocks}
+           "gpu_launches": int(launches), "clocks": clocks, "issue_roofline": issue}
 
     # ---- CPU baseline on this box's host cores (bounded sample), rank 0 at N = 1 only
     if world == 1:
