@@ -150,3 +150,22 @@ def test_estimator_params(fd):
     imp = fd.RandomForestClassificationModel([fd.spark_format.TreeArrays([2, -1, -1], [0.5, 0, 0], [1, -1, -1], [2, -1, -1], [0, 0, 1],
                                                                          [[5, 5], [5, 0], [0, 5]], gain=[0.5, -1, -1])], 4).featureImportances
     assert imp.tolist() == [0.0, 0.0, 1.0, 0.0]
+
+
+def test_hostmem_helpers_without_a_gpu(fd):
+    """The NUMA helper parses sysfs cpulists and is a no-op (affinity untouched) when the node cannot be determined."""
+    import os
+    hostmem = importlib.import_module("fraud-detection-spark-kafka-llm_b200.hostmem")
+    assert hostmem._parse_cpulist("0-3,8,10-11\n") == [0, 1, 2, 3, 8, 10, 11] and hostmem._parse_cpulist("") == []
+    assert hostmem.node_cpus(10 ** 6) == []
+    before = os.sched_getaffinity(0)
+    orig = hostmem.gpu_numa_node
+    hostmem.gpu_numa_node = lambda device: None
+    try:
+        rep = {}
+        with fd.numa_local(0, rep) as info:
+            assert info["bound"] is False and os.sched_getaffinity(0) == before
+        assert rep == {"node": None, "bound": False}
+    finally:
+        hostmem.gpu_numa_node = orig
+    assert os.sched_getaffinity(0) == before
