@@ -193,6 +193,78 @@ def gini(counts: Sequence[float]) -> float:
     return imp
 
 
+def _gini_rows(stats: np.ndarray) -> np.ndarray:
+    """:func:`gini` over the rows of ``stats`` [m, 2], same operation order (1 - f0*f0 - f1*f1, 0 when the row is empty)."""
+    total = stats[:, 0] + stats[:, 1]
+    safe = np.where(total == 0.0, 1.0, total)
+    f0, f1 = stats[:, 0] / safe, stats[:, 1] / safe
+    return np.where(total == 0.0, 0.0, (1.0 - f0 * f0) - f1 * f1)
+
+
+def trees_from_levels(n_trees: int, tree: np.ndarray, heap: np.ndarray, stats: np.ndarray, split: np.ndarray, feature: np.ndarray,
+                      threshold: np.ndarray, gain: np.ndarray, prune: bool) -> List[sf.TreeArrays]:
+    """``LearningNode.toNode(prune)`` for a whole forest at once.  One row per grown node: its tree, heap id (root 1,
+    children 2n / 2n+1), class counts, and -- where ``split`` -- the split it received.  With ``prune`` a split whose
+    two (pruned) children are leaves predicting the same class collapses into a leaf, bottom-up.  Returns each tree
+    in Spark's pre-order numbering."""
+    tree = np.asarray(tree, dtype=np.int64)
+    heap = np.asarray(heap, dtype=np.int64)
+    n = tree.size
+    depth = np.zeros(n, dtype=np.int64)
+    tmp = heap.copy()
+    while True:
+        tmp >>= 1
+        more = tmp > 0
+        if not more.any():
+            break
+        depth += more
+    maxd = int(depth.max()) if n else 0
+    key = (tree << 32) | heap
+    by_key = np.argsort(key, kind="stable")
+    skey = key[by_key]
+
+    def index_of(t, h):  # row index of node (t, h); every queried node exists
+        return by_key[np.searchsorted(skey, (t << 32) | h)]
+
+    pred = (stats[:, 1] > stats[:, 0]).astype(np.int64)
+    leaf = ~np.asarray(split, dtype=bool)
+    if prune:
+        for d in range(maxd - 1, -1, -1):
+            cand = np.nonzero((depth == d) & ~leaf)[0]
+            if cand.size == 0:
+                continue
+            li, ri = index_of(tree[cand], 2 * heap[cand]), index_of(tree[cand], 2 * heap[cand] + 1)
+            leaf[cand[leaf[li] & leaf[ri] & (pred[li] == pred[ri])]] = True
+    kept = depth == 0
+    for d in range(1, maxd + 1):
+        cand = np.nonzero(depth == d)[0]
+        if cand.size == 0:
+            continue
+        par = index_of(tree[cand], heap[cand] >> 1)
+        kept[cand[kept[par] & ~leaf[par]]] = True
+    rows = np.nonzero(kept)[0]
+    # pre-order = paths in lexicographic order with an ancestor before its descendants: heap ids left-aligned, then depth
+    aligned = heap[rows] << (maxd - depth[rows])
+    rows = rows[np.lexsort((depth[rows], aligned, tree[rows]))]
+    t_sorted = tree[rows]
+    starts = np.searchsorted(t_sorted, np.arange(n_trees + 1))
+    pos = np.empty(n, dtype=np.int64)
+    pos[rows] = np.arange(rows.size) - starts[t_sorted]
+    inner = rows[~leaf[rows]]
+    left = np.full(n, -1, dtype=np.int64)
+    right = np.full(n, -1, dtype=np.int64)
+    left[inner] = pos[index_of(tree[inner], 2 * heap[inner])]
+    right[inner] = pos[index_of(tree[inner], 2 * heap[inner] + 1)]
+    imp = _gini_rows(stats)
+    out = []
+    for t in range(n_trees):
+        r = rows[starts[t]:starts[t + 1]]
+        lf = leaf[r]
+        out.append(sf.TreeArrays(np.where(lf, -1, feature[r]), np.where(lf, 0.0, threshold[r]), left[r], right[r], pred[r].astype(np.float64),
+                                 stats[r], imp[r], np.where(lf, -1.0, gain[r])))
+    return out
+
+
 def features_per_node(strategy: str, n_trees: int, n_features: int) -> int:
     """``DecisionTreeMetadata.numFeaturesPerNode`` for classification."""
     s = strategy.lower()
@@ -482,35 +554,47 @@ class ForestTrainer:
         batch_fn = default_subset_batch(self.seed, self.F, k, dev) if subset_fn is None else None
         d_col_len = csc[0][1:] - csc[0][:-1]
         tt = self._tick("bagging+root", tt)
-        # ---- level-wise growth; nodes[t][heap id] = record
-        nodes: List[Dict[int, dict]] = [{1: {"stats": [float(root[t, 0]), float(root[t, 1])], "leaf": True}} for t in range(self.T)]
-        frontier = [(t, 1) for t in range(self.T)]
+        # ---- level-wise growth.  Host bookkeeping is array-valued: one record per grown node, kept per level
+        #      (tree, heap id, class counts, and -- once it splits -- feature / threshold / gain)
+        lt = np.arange(self.T, dtype=np.int32)                  # this level's nodes: tree ...
+        ln = np.ones(self.T, dtype=np.int32)                    # ... heap id (root 1) ...
+        ls = np.ascontiguousarray(root, dtype=np.float64)       # ... class counts [m, 2]
+        levels = []
         hist_bytes = allreduce_calls = 0
-        for depth in range(self.max_depth):
-            base = 1 << depth
-            active = [(t, n) for (t, n) in frontier if depth == 0 or abs(gini(nodes[t][n]["stats"])) >= EPSILON]
-            if not active:
+        for depth in range(self.max_depth + 1):
+            m_lvl = lt.size
+            l_split = np.zeros(m_lvl, dtype=bool)
+            l_feat = np.full(m_lvl, -1, dtype=np.int32)
+            l_thr = np.zeros(m_lvl, dtype=np.float64)
+            l_gain = np.full(m_lvl, -1.0, dtype=np.float64)
+            levels.append((lt, ln, ls, l_split, l_feat, l_thr, l_gain))
+            if depth == self.max_depth or m_lvl == 0:
                 break
-            splits = []  # (t, n, f, bin)
-            next_frontier = []
+            base = 1 << depth
+            aidx = np.arange(m_lvl) if depth == 0 else np.nonzero(np.abs(_gini_rows(ls)) >= EPSILON)[0]
+            if aidx.size == 0:
+                break
+            sp_parts, child_parts = [], []
             g0 = 0
-            while g0 < len(active):
+            while g0 < aidx.size:
                 # ---- one node group: items = node x feature subset (features without thresholds dropped), on the device
                 g1 = g0
                 if batch_fn is not None:
                     per_node = max(1, min(k, self.F))
-                    g1 = min(len(active), g0 + max(1, MAX_ITEMS_PER_GROUP // per_node))
-                    grp = torch.tensor(active[g0:g1], dtype=torch.int32, device=dev)
+                    g1 = min(aidx.size, g0 + max(1, MAX_ITEMS_PER_GROUP // per_node))
+                    gi = aidx[g0:g1]
+                    grp_t = torch.from_numpy(lt[gi]).to(dev)
+                    grp_n = torch.from_numpy(ln[gi]).to(dev)
                     sub = batch_fn(depth, g0, g1 - g0)                           # [m, k]
                     ok = d_nsplits[sub] > 0
                     cnt = ok.sum(dim=1)
-                    items = (torch.repeat_interleave(grp[:, 0], cnt), torch.repeat_interleave(grp[:, 1], cnt), sub[ok].to(torch.int32))
+                    items = (torch.repeat_interleave(grp_t, cnt), torch.repeat_interleave(grp_n, cnt), sub[ok].to(torch.int32))
                     d_ptr = torch.zeros(g1 - g0 + 1, dtype=torch.int32, device=dev)
                     d_ptr[1:] = torch.cumsum(cnt, 0)
                 else:
                     it_t, it_n, it_f, ptr = [], [], [], [0]
-                    while g1 < len(active) and (g1 == g0 or ptr[-1] < MAX_ITEMS_PER_GROUP):
-                        t, n = active[g1]
+                    while g1 < aidx.size and (g1 == g0 or ptr[-1] < MAX_ITEMS_PER_GROUP):
+                        t, n = int(lt[aidx[g1]]), int(ln[aidx[g1]])
                         feats = np.asarray(subset_fn(t, n), dtype=np.int32)
                         feats = feats[n_splits[feats] > 0]
                         it_t.append(np.full(feats.size, t, np.int32))
@@ -518,9 +602,9 @@ class ForestTrainer:
                         it_f.append(feats)
                         ptr.append(ptr[-1] + feats.size)
                         g1 += 1
+                    gi = aidx[g0:g1]
                     items = tuple(torch.from_numpy(np.concatenate(x)).to(dev) for x in (it_t, it_n, it_f))
                     d_ptr = torch.tensor(ptr, dtype=torch.int32, device=dev)
-                group = active[g0:g1]
                 g0 = g1
                 tt = self._tick("subsets+items", tt)
                 if items[2].numel() == 0:
@@ -534,67 +618,40 @@ class ForestTrainer:
                     allreduce_calls += 1
                 hist_bytes += hist.numel() * 4
                 tt = self._tick("allreduce", tt)
-                totals = torch.tensor([nodes[t][n]["stats"] for (t, n) in group], dtype=torch.float64, device=dev)
+                totals = torch.from_numpy(np.ascontiguousarray(ls[gi])).to(dev)
                 bi, bs, bg, left, right = self.b.best_split(hist, d_ptr, items[2], totals, d_nsplits, d_bz, self.min_instances,
                                                             self.min_info_gain)
                 bf = items[2][bi.clamp(min=0).long()]  # feature of the winning item
                 bi, bs, bg, left, right, bf = (x.cpu().numpy() for x in (bi, bs, bg, left, right, bf))
                 del hist
                 tt = self._tick("kernel:best_split+d2h", tt)
-                for j, (t, n) in enumerate(group):
-                    if bi[j] < 0 or not (bg[j] > 0.0):
-                        continue  # stays a leaf
-                    f = int(bf[j])
-                    sb = int(bs[j])
-                    rec = nodes[t][n]
-                    rec.update(leaf=False, feature=f, split_bin=sb, threshold=float(thr[thr_ptr[f] + sb]), gain=float(bg[j]))
-                    nodes[t][2 * n] = {"stats": [float(left[j, 0]), float(left[j, 1])], "leaf": True}
-                    nodes[t][2 * n + 1] = {"stats": [float(right[j, 0]), float(right[j, 1])], "leaf": True}
-                    splits.append((t, n, f, sb))
-                    next_frontier += [(t, 2 * n), (t, 2 * n + 1)]
+                won = (bi >= 0) & (bg > 0.0)             # the others stay leaves
+                wi = gi[won]
+                f, sb = bf[won].astype(np.int32), bs[won].astype(np.int32)
+                l_split[wi] = True
+                l_feat[wi] = f
+                l_thr[wi] = thr[thr_ptr[f] + sb]
+                l_gain[wi] = bg[won]
+                sp_parts.append(np.stack([lt[wi], ln[wi], f, sb], 1).astype(np.int32))
+                child_parts.append((lt[wi], ln[wi], left[won], right[won]))
             tt = self._tick("host:grow", tt)
-            if not splits:
+            sp = np.concatenate(sp_parts) if sp_parts else np.zeros((0, 4), np.int32)
+            if sp.shape[0] == 0:
                 break
-            sp = np.asarray(splits, dtype=np.int32)
             action = np.full((self.T, base), -1, dtype=np.int32)
             action[sp[:, 0], sp[:, 1] - base] = np.where(bin_of_zero[sp[:, 2]] <= sp[:, 3], 2 * sp[:, 1], 2 * sp[:, 1] + 1)
             d_sp = tuple(torch.from_numpy(np.ascontiguousarray(sp[:, c])).to(dev) for c in range(4))
             units = tuple(torch.from_numpy(a).to(dev) for a in _units(col_len, sp[:, 2]))
             self.b.advance(csc, state, base, d_sp, units, torch.from_numpy(action).to(dev))
-            frontier = next_frontier
+            # next level: the two children of every split node, left then right, in split order
+            ct = np.concatenate([c[0] for c in child_parts])
+            cn = np.concatenate([c[1] for c in child_parts])
+            cl = np.concatenate([c[2] for c in child_parts])
+            cr = np.concatenate([c[3] for c in child_parts])
+            lt = np.repeat(ct, 2).astype(np.int32)
+            ln = np.stack([2 * cn, 2 * cn + 1], 1).reshape(-1).astype(np.int32)
+            ls = np.stack([cl, cr], 1).reshape(-1, 2).astype(np.float64)
             tt = self._tick("kernel:advance", tt)
         self.stats = {"phases_s": dict(self._t), "hist_bytes": float(hist_bytes), "allreduce_calls": float(allreduce_calls), "n_total": float(n_total)}
-        return [self._to_tree(nd) for nd in nodes]
-
-    # -- LearningNode.toNode(prune): heap-indexed records -> pre-order arrays
-    def _to_tree(self, nd: Dict[int, dict]) -> sf.TreeArrays:
-        def build(i):
-            r = nd[i]
-            pred = 1 if r["stats"][1] > r["stats"][0] else 0
-            if r["leaf"]:
-                return dict(leaf=True, rec=r, pred=pred)
-            l, rr = build(2 * i), build(2 * i + 1)
-            if self.prune and l["leaf"] and rr["leaf"] and l["pred"] == rr["pred"]:
-                return dict(leaf=True, rec=r, pred=pred)
-            return dict(leaf=False, rec=r, pred=pred, l=l, r=rr)
-
-        feature, threshold, left, right, pred, stats, imp, gain = [], [], [], [], [], [], [], []
-
-        def emit(x):
-            me = len(feature)
-            r = x["rec"]
-            feature.append(-1 if x["leaf"] else r["feature"])
-            threshold.append(0.0 if x["leaf"] else r["threshold"])
-            left.append(-1)
-            right.append(-1)
-            pred.append(float(x["pred"]))
-            stats.append(list(r["stats"]))
-            imp.append(gini(r["stats"]))
-            gain.append(-1.0 if x["leaf"] else r["gain"])
-            if not x["leaf"]:
-                left[me] = emit(x["l"])
-                right[me] = emit(x["r"])
-            return me
-
-        emit(build(1))
-        return sf.TreeArrays(feature, threshold, left, right, pred, np.asarray(stats, dtype=np.float64), imp, gain)
+        cat = [np.concatenate([lv[c] for lv in levels]) for c in range(7)]
+        return trees_from_levels(self.T, cat[0], cat[1], cat[2], cat[3], cat[4], cat[5], cat[6], self.prune)

@@ -157,3 +157,67 @@ def test_oracle_stump_gain_agrees_with_sklearn(seed):
     if int(tree.feature[0]) == int(sk.feature[0]):
         # same partition of the training rows (sklearn stores the midpoint rounded to float32-representable doubles)
         assert np.array_equal(dense[:, sk.feature[0]] <= sk.threshold[0], dense[:, tree.feature[0]] <= tree.threshold[0])
+
+
+@pytest.mark.parametrize("prune", [True, False])
+def test_trees_from_levels_matches_a_recursive_builder(prune):
+    """The forest builder (heap-indexed node rows -> Spark's pre-order arrays, with LearningNode.toNode's pruning) against
+    a plain recursive restatement, on random ragged forests given in random row order."""
+    rng = np.random.default_rng(5 + prune)
+    for _ in range(25):
+        T = int(rng.integers(1, 6))
+        recs, rows = [dict() for _ in range(T)], []
+        for t in range(T):
+            def grow(h, d):
+                st = [float(rng.integers(0, 5)), float(rng.integers(0, 5))]
+                sp = d < 6 and rng.random() < (0.75 if d < 3 else 0.5)
+                r = dict(stats=st, split=sp, feature=int(rng.integers(0, 100)) if sp else -1, threshold=float(rng.random()) if sp else 0.0,
+                         gain=float(rng.random()) if sp else -1.0)
+                recs[t][h] = r
+                rows.append((t, h, st, sp, r["feature"], r["threshold"], r["gain"]))
+                if sp:
+                    grow(2 * h, d + 1)
+                    grow(2 * h + 1, d + 1)
+            grow(1, 0)
+
+        def reference(nd):
+            def build(i):
+                r = nd[i]
+                pred = 1 if r["stats"][1] > r["stats"][0] else 0
+                if not r["split"]:
+                    return dict(leaf=True, rec=r, pred=pred)
+                l, rr = build(2 * i), build(2 * i + 1)
+                if prune and l["leaf"] and rr["leaf"] and l["pred"] == rr["pred"]:
+                    return dict(leaf=True, rec=r, pred=pred)
+                return dict(leaf=False, rec=r, pred=pred, l=l, r=rr)
+            out = dict(feature=[], threshold=[], left=[], right=[], pred=[], stats=[], gain=[])
+
+            def emit(x):
+                me = len(out["feature"])
+                r = x["rec"]
+                out["feature"].append(-1 if x["leaf"] else r["feature"])
+                out["threshold"].append(0.0 if x["leaf"] else r["threshold"])
+                out["left"].append(-1)
+                out["right"].append(-1)
+                out["pred"].append(float(x["pred"]))
+                out["stats"].append(r["stats"])
+                out["gain"].append(-1.0 if x["leaf"] else r["gain"])
+                if not x["leaf"]:
+                    out["left"][me] = emit(x["l"])
+                    out["right"][me] = emit(x["r"])
+                return me
+            emit(build(1))
+            return out
+
+        order = rng.permutation(len(rows))
+        R = [rows[i] for i in order]
+        got = training.trees_from_levels(T, np.array([r[0] for r in R]), np.array([r[1] for r in R]), np.array([r[2] for r in R], dtype=np.float64),
+                                         np.array([r[3] for r in R]), np.array([r[4] for r in R]), np.array([r[5] for r in R]),
+                                         np.array([r[6] for r in R]), prune)
+        for t in range(T):
+            exp = reference(recs[t])
+            g = got[t]
+            assert g.feature.tolist() == exp["feature"] and g.threshold.tolist() == exp["threshold"]
+            assert g.left.tolist() == exp["left"] and g.right.tolist() == exp["right"]
+            assert g.prediction.tolist() == exp["pred"] and g.stats.tolist() == exp["stats"] and g.gain.tolist() == exp["gain"]
+            assert g.impurity.tolist() == [training.gini(s_) for s_ in exp["stats"]]
