@@ -257,16 +257,18 @@ __global__ void __launch_bounds__(256) k_rf_advance_explicit(const int64_t* __re
     }
 }
 
-__global__ void k_rf_advance_default(uint32_t* __restrict__ state, long long n_rows, int n_trees, int level_base,
+__global__ void k_rf_advance_default(uint32_t* __restrict__ state, long long n_rows, int level_base,
                                      const int32_t* __restrict__ action) {
-    const long long total = n_rows * n_trees;
+    // blockIdx.y = tree: no 64-bit division per element, and the tree's action row is read through one pointer
+    uint32_t* st = state + (long long)blockIdx.y * n_rows;
+    const int32_t* act = action + (long long)blockIdx.y * level_base;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
-        const uint32_t v = state[k];
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n_rows; k += stride) {
+        const uint32_t v = st[k];
         const int n = (int)(v >> 8);
         if (n >= level_base && n < 2 * level_base) {
-            const int a = action[(k / n_rows) * level_base + (n - level_base)];
-            if (a >= 0) state[k] = ((uint32_t)a << 8) | (v & 255u);
+            const int a = act[n - level_base];
+            if (a >= 0) st[k] = ((uint32_t)a << 8) | (v & 255u);
         }
     }
 }
@@ -374,10 +376,12 @@ int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowid
                                                  seg_len, split_tree_dev, split_node_dev, split_feat_dev, split_bin_dev);
         h->launches += 1;
     }
-    long long total = n_rows * n_trees;
-    long long g2 = (total + 255) / 256;
-    if (g2 > (long long)h->sm_count * 16) g2 = (long long)h->sm_count * 16;
-    k_rf_advance_default<<<(unsigned)g2, 256, 0, st>>>(state_dev, n_rows, n_trees, level_base, action_dev);
+    long long g2 = (n_rows + 255) / 256;
+    const long long cap = std::max<long long>(1, (long long)h->sm_count * 16 / std::max(1, n_trees));
+    if (g2 > cap) g2 = cap;
+    if (g2 < 1) g2 = 1;
+    if (n_trees > 65535) return set_err(h, FD_ERR_LIMIT, "at most 65535 trees per advance call");
+    k_rf_advance_default<<<dim3((unsigned)g2, (unsigned)n_trees), 256, 0, st>>>(state_dev, n_rows, level_base, action_dev);
     h->launches += 1;
     FD_CUDA(h, cudaGetLastError());
     return FD_OK;

@@ -520,10 +520,10 @@ class ForestTrainer:
         if self.max_depth > 22:
             raise ValueError("maxDepth > 22 is not supported (node ids share a 32-bit word with the bag weight)")
         # column entries carry (row | label << 31): the histogram kernel then needs a single gather per entry
-        row_lab = row_of | (labels.to(torch.int32) << 31)[row_of.long()]
+        row_lab = row_of | torch.repeat_interleave(labels.to(torch.int32) << 31, counts)
         csc = (torch.zeros(self.F + 1, dtype=torch.int64, device=dev), row_lab[order].contiguous(), bins[order].contiguous())
         del row_lab
-        torch.cumsum(torch.bincount(idx.long(), minlength=self.F), 0, out=csc[0][1:])
+        torch.cumsum(torch.bincount(idx, minlength=self.F), 0, out=csc[0][1:])
         col_len = np.diff(csc[0].cpu().numpy())
         del order, row_of, bins
         tt = self._tick("bin+csc", tt)
