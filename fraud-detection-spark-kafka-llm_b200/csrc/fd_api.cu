@@ -459,6 +459,8 @@ int fd_set_vocabulary(fd_handle* h, const uint8_t* words, const int32_t* offs, i
     m.vocab_cap = cap;
     m.num_features = n_words;
     m.binary = binary ? 1 : 0;
+    m.used_on = 0;    // bitmaps sized for another feature space are not consulted (set the classifier after the featuriser)
+    m.lr_sparse = 0;
     m.mod_pow2 = 0;
     m.empty_absent = empty_id < 0;
     m.empty_idx = empty_id < 0 ? 0u : (uint32_t)empty_id;

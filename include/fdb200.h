@@ -62,6 +62,10 @@ const char* fd_last_error(fd_handle* h);
 int fd_version(void);
 
 /* ---- model upload (host pointers, synchronous) ---------------------------------------------- */
+/* Order: featuriser first (stop words, then HashingTF or the vocabulary), IDF, classifier last -- as the stages of the
+ * saved pipeline come.  The classifier upload derives per-feature tables (quantised thresholds, the bitmaps of features the
+ * model can see) from the feature space and the IDF vector in force; changing the featuriser afterwards switches those
+ * bitmaps off until the classifier is set again. */
 /* StopWordsRemover params (stages/1_StopWordsRemover_8c0b00b256b3/metadata/part-00000:1).
  * words = UTF-8 bytes back to back, offs = int32[n_words+1].  With case_sensitive == 0 ASCII
  * letters of the list are folded to lower case (the host folds non-ASCII ones before the call). */
