@@ -11,14 +11,16 @@ static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 constexpr size_t SLOT_CTRL = 256;
 constexpr size_t SLOT_BIGTABS = wide_pool_slots(MED_CTAS, BIG_WORKERS) * 8;
-// scratch slot = control block, wide tables, then the deferred-dialogue list with ONE ENTRY PER DIALOGUE of the
+// scratch slot = control block, wide tables, per-warp spill tables, then the deferred-dialogue list with ONE ENTRY PER DIALOGUE of the
 // call (every dialogue may be deferred, so the list can never overflow)
-static size_t slot_bytes(long long n_rows) { return align_up(SLOT_CTRL + SLOT_BIGTABS + (size_t)n_rows * 8, 256); }
+constexpr size_t SLOT_SPILL = SPILL_SLOTS * 8;
+static size_t slot_bytes(long long n_rows) { return align_up(SLOT_CTRL + SLOT_BIGTABS + SLOT_SPILL + (size_t)n_rows * 8, 256); }
 
 static void fill_slot(RowArgs& a, char* base, long long n_rows) {
     a.ctrl = reinterpret_cast<Ctrl*>(base);
     a.big_tabs = reinterpret_cast<unsigned long long*>(base + SLOT_CTRL);
-    a.big_rows = reinterpret_cast<long long*>(base + SLOT_CTRL + SLOT_BIGTABS);
+    a.spill_tabs = reinterpret_cast<unsigned long long*>(base + SLOT_CTRL + SLOT_BIGTABS);
+    a.big_rows = reinterpret_cast<long long*>(base + SLOT_CTRL + SLOT_BIGTABS + SLOT_SPILL);
     a.big_cap = n_rows;
 }
 

@@ -91,6 +91,7 @@ extern "C" int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const
     a.m = h->m;  // (after prepare_fused)
     a.ctrl = reinterpret_cast<Ctrl*>(base);
     a.big_tabs = reinterpret_cast<unsigned long long*>(base + NA_CTRL);
+    a.spill_tabs = nullptr;  // (a fixed scratch array cannot hold a table per warp: overflowing dialogues are deferred)
     a.big_rows = reinterpret_cast<long long*>(base + NA_CTRL + NA_TABS);
     a.big_cap = NOALLOC_MAX_ROWS;
     a.pred = out_pred_dev;

@@ -667,8 +667,24 @@ k_rows(const RowArgs a) {
             constexpr int TPL = 1;  // tokens per lane per iteration (2 was measured slower: more idle lanes in the last iteration, 79 registers)
             for (int t0 = t_first; t0 < Tc; t0 += 32 * TPL) {
                 if (D + 32u * TPL > (3u << TLOG2) / 4u) {  // keep the table at most 3/4 full
-                    big = true;
-                    break;
+                    const long long gw = (long long)blockIdx.x * ROW_WARPS + warp;
+                    if (TL == 9 && BIG == 0 && tab == S.tab && a.spill_tabs != nullptr && gw < SPILL_WARPS) {
+                        // carry on in this warp's own wide table: clear it, move the entries over, switch
+                        unsigned long long* wt = a.spill_tabs + ((size_t)gw << MED_LOG2);
+                        const uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);
+                        for (int i = lane; i < (1 << MED_LOG2) / 2; i += 32) reinterpret_cast<uint4*>(wt)[i] = ff;
+                        __syncwarp();
+                        for (int i = lane; i < (1 << TAB_LOG2); i += 32) {
+                            const unsigned long long e = S.tab[i];
+                            if ((uint32_t)(e >> 32) != EMPTY_KEY) tab_insert(wt, MED_LOG2, (uint32_t)(e >> 32), (uint32_t)e, false);
+                        }
+                        __syncwarp();
+                        tab = wt;
+                        TLOG2 = MED_LOG2;
+                    } else {
+                        big = true;
+                        break;
+                    }
                 }
                 // The body is written in warp-uniform phases (boundaries -> hash -> stop-word lookup -> insert)
                 // with per-lane predicates instead of nested branches, so the 64 tokens stay in lock step.
@@ -849,11 +865,15 @@ k_rows(const RowArgs a) {
                     }
                 }
             } else {
-                row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), reinterpret_cast<double*>(rb), BIG == 0, tab, TLOG2, row, (int)D, lane);
+                row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), reinterpret_cast<double*>(rb), BIG == 0 && tab == S.tab, tab, TLOG2, row, (int)D, lane);
             }
             // reset the table and the per-dialogue state
             __syncwarp();
             if (BIG && have_next) TLOG2 = wide_table_log2(n_end - n_beg);
+            if (TL == 9 && BIG == 0 && tab != S.tab) {  // back to the shared-memory table for the next dialogue
+                tab = S.tab;
+                TLOG2 = TAB_LOG2;
+            }
             if (dts) {
                 const uint4 z = make_uint4(0u, 0u, 0u, 0u);
                 for (int i = lane; i < (1 << m.dt_log2) / 4; i += 32) reinterpret_cast<uint4*>(tab)[i] = z;

@@ -26,6 +26,11 @@ constexpr int MED_WARPS = 8;
 constexpr int MED_CTAS = 296;
 constexpr int BIG_LOG2 = 16;
 constexpr int BIG_WORKERS = 148;
+// Micro-batch / long-dialogue shape (TL = 9): a warp whose shared-memory table fills up carries on in its OWN 2^MED_LOG2-slot
+// table in global memory (the entries move over, the dialogue is not restarted); only dialogues that outgrow that one as
+// well are deferred.  One table per warp of the grid, SPILL_WARPS at most.
+constexpr int SPILL_WARPS = 160 * 3 * 8;
+constexpr size_t SPILL_SLOTS = (size_t)SPILL_WARPS << MED_LOG2;
 constexpr size_t wide_pool_slots(int med_ctas, int big_workers) {
     return ((size_t)med_ctas * MED_WARPS << MED_LOG2) > ((size_t)big_workers << BIG_LOG2) ? ((size_t)med_ctas * MED_WARPS << MED_LOG2)
                                                                                          : ((size_t)big_workers << BIG_LOG2);
@@ -54,6 +59,7 @@ struct RowArgs {
     long long big_cap;
     int pick_shape;  // 1: both main-kernel shapes are launched and ctrl->shape says which one runs
     unsigned long long* big_tabs;
+    unsigned long long* spill_tabs;  // SPILL_SLOTS slots, or nullptr (no spilling: overflowing dialogues are deferred)
     // featurize outputs (staging)
     int32_t* row_nnz;
     long long* row_tmpoff;
