@@ -833,7 +833,11 @@ k_rows(const RowArgs a) {
                         ins = fi != NOT_IN_VOCAB;
                     }
                     bool isnew = false;
-                    if (ins) isnew = count_term<MODE>(a, tab, TLOG2, fi, 1u, binary);
+                    if (BIG == 0 && tab == S.tab) {  // (named so that the common case keeps shared-memory atomics)
+                        if (ins) isnew = count_term<MODE>(a, S.tab, TAB_LOG2, fi, 1u, binary);
+                    } else {
+                        if (ins) isnew = count_term<MODE>(a, tab, TLOG2, fi, 1u, binary);
+                    }
                     D += __popc(__ballot_sync(0xFFFFFFFFu, isnew));
                     pend += __popc(__ballot_sync(0xFFFFFFFFu, empty[u] && !interior_empty));
                 }
@@ -865,7 +869,10 @@ k_rows(const RowArgs a) {
                     }
                 }
             } else {
-                row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), reinterpret_cast<double*>(rb), BIG == 0 && tab == S.tab, tab, TLOG2, row, (int)D, lane);
+                if (BIG == 0 && tab == S.tab)
+                    row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), reinterpret_cast<double*>(rb), true, S.tab, TAB_LOG2, row, (int)D, lane);
+                else
+                    row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), reinterpret_cast<double*>(rb), false, tab, TLOG2, row, (int)D, lane);
             }
             // reset the table and the per-dialogue state
             __syncwarp();
