@@ -99,7 +99,9 @@ def build_workload(fd, rows, tokens, device, seed, featurizer="gpu"):
                    fd.HashingTF(inputCol="filtered_words", outputCol="raw_features", numFeatures=nf)]
     # IDF fitted on a 65,536-dialogue sample of the same corpus
     ns = min(rows, 1 << 16)
-    words = corpus.words[corpus.n_stop:corpus.n_stop + 12] + [b""]
+    # the tree splits on features drawn from the 2,000 most frequent buckets (plus the empty token), in
+    # proportion to their document frequency, as a trained tree prefers words that occur -- so that paths actually branch
+    words = corpus.words[corpus.n_stop:corpus.n_stop + 2000] + [b""]
     if featurizer == "gpu":
         tf_model = fd.PipelineModel(feat_stages)
         sample = fd.PackedText(pk.data, pk.offs[:ns + 1])
@@ -120,7 +122,7 @@ def build_workload(fd, rows, tokens, device, seed, featurizer="gpu"):
         top = np.asarray([so.hashing_tf_index(w, nf) for w in words], dtype=np.int64)
     idf_model = fd.IDF(inputCol="raw_features", outputCol="features").fit_from_doc_freq(df, ns)
     rng = np.random.default_rng(seed)
-    tree = synth.random_tree(rng, 5, top, idf_model.idf)
+    tree = synth.random_tree(rng, 5, top, idf_model.idf, weights=np.asarray(df)[top])
     model = fd.PipelineModel(feat_stages + [idf_model, fd.DecisionTreeClassificationModel(tree, nf)])
     total_bytes = int(pk.offs[-1].item() - pk.offs[0].item())
     stats = {"L_bar": total_bytes / rows, "nnz_bar": nnz_bar, "text_bytes": total_bytes}

@@ -5,6 +5,8 @@
 #include <cstring>
 #include <cmath>
 #include <algorithm>
+#include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "fd_rows.cuh"
@@ -54,12 +56,48 @@ static int upload(fd_handle* h, T** dst, const T* src, size_t n);
 // The quantised forest is laid out two levels per 32-byte record (Model::nodes_s): a walk is bound by the L2 -> L1
 // sector traffic of its node fetches (one 32-byte sector per fetch whatever the node size), so a record carries a
 // split node AND both its children and one fetch decides two levels.
+// features the stop words map to under the current featuriser (hashing trick or vocabulary)
+static std::vector<uint32_t> stop_word_features(const fd_handle* h) {
+    std::vector<uint32_t> out;
+    const Model& m = h->m;
+    if (m.num_features <= 0) return out;
+    std::unordered_map<std::string, uint32_t> vocab;
+    for (size_t i = 0; i < h->host_vocab.size(); ++i)
+        vocab.emplace(std::string(h->host_vocab[i].begin(), h->host_vocab[i].end()), (uint32_t)i);
+    for (const auto& w : h->host_stop) {
+        if (!h->host_vocab.empty()) {
+            auto it = vocab.find(std::string(w.begin(), w.end()));
+            if (it != vocab.end()) out.push_back(it->second);
+        } else {
+            out.push_back(nonneg_mod_host(murmur3_host(w.data(), (int)w.size()), m.num_features));
+        }
+    }
+    std::sort(out.begin(), out.end());
+    out.erase(std::unique(out.begin(), out.end()), out.end());
+    return out;
+}
+
 int prepare_fused(fd_handle* h) {
     if (!h->fused_dirty) return FD_OK;
     Model& m = h->m;
     h->fused_dirty = false;
     m.int_walk = 0;
     m.dt_small = 0;
+    m.dt_heap_on = 0;
+    m.filt_on = 0;
+    const std::vector<uint32_t> stop_feats = stop_word_features(h);
+    // (1) what the classifier can see, and which of those features a stop word maps to
+    const size_t nwords = ((size_t)std::max(m.num_features, 1) + 31) / 32;
+    if (m.classifier != 0 && h->filt_want && h->host_seen.size() == nwords) {
+        std::vector<uint2> filt(nwords);
+        for (size_t i = 0; i < nwords; ++i) filt[i] = make_uint2(h->host_seen[i], 0u);
+        for (uint32_t f : stop_feats)
+            if ((size_t)(f >> 5) < nwords) filt[f >> 5].y |= filt[f >> 5].x & (1u << (f & 31));
+        int rcf = upload(h, &m.filt, filt.data(), filt.size());
+        if (rcf) return rcf;
+        m.filt_on = 1;
+    }
+    // (2) forests: thresholds quantised to term counts, two levels per record
     if (m.classifier != 2 || h->host_nodes.empty()) return FD_OK;
     const bool has_idf = !h->host_idf.empty();
     const std::vector<Node>& q = h->host_nodes;
@@ -119,7 +157,6 @@ int prepare_fused(fd_handle* h) {
     if (rc) return rc;
     m.int_walk = 1;
     // decision tree: count only the split features (Model::dt_small)
-    m.dt_small = 0;
     if (m.kind == FD_KIND_DT) {
         std::vector<uint32_t> feats;
         for (const auto& nd : q)
@@ -148,9 +185,45 @@ int prepare_fused(fd_handle* h) {
                 if (found) break;
             }
         }
+        // the main kernel's ballot walk needs the tree in heap order, at most 5 levels of split nodes
+        std::vector<int2> heap(32, make_int2(0, 0x7FFFFFFF));
+        std::vector<double> outv(32 * 5, 0.0);
+        bool shallow = found;
+        if (found) {
+            std::vector<int> at(63, -1);  // heap position -> node index
+            at[0] = h->host_root0;
+            for (int p = 0; p < 63 && shallow; ++p) {
+                const int n = at[p];
+                const bool leaf = is_leaf(n);
+                if (p >= 31) {
+                    if (!leaf) shallow = false;
+                    continue;
+                }
+                if (leaf) {
+                    at[2 * p + 1] = at[2 * p + 2] = n;  // positions below a leaf repeat it ("go left" from an absent node)
+                } else {
+                    heap[(size_t)p] = make_int2((int)(((uint32_t)q[(size_t)n].feat * mul) >> (32 - lg)), cs[(size_t)n]);
+                    at[2 * p + 1] = q[(size_t)n].child;
+                    at[2 * p + 2] = q[(size_t)n].child + 1;
+                }
+            }
+            if (shallow) {
+                for (int p = 31; p < 63; ++p) {
+                    const size_t n = (size_t)at[p];
+                    const double2 st = h->host_leaf2[n], pr = h->host_leafp[n];
+                    double* o = &outv[(size_t)(p - 31) * 5];
+                    o[0] = st.y > st.x ? 1.0 : 0.0;
+                    o[1] = pr.x;
+                    o[2] = pr.y;
+                    o[3] = st.x;
+                    o[4] = st.y;
+                }
+            }
+        }
         if (found) {
             std::vector<uint32_t> dtab((size_t)1 << lg, 0xFFFFFFFFu);
-            for (uint32_t f : feats) dtab[(f * mul) >> (32 - lg)] = f;
+            for (uint32_t f : feats)
+                dtab[(f * mul) >> (32 - lg)] = f | (std::binary_search(stop_feats.begin(), stop_feats.end(), f) ? 0x80000000u : 0u);
             std::vector<uint32_t> sec_dt = sec;
             for (size_t n = 0; n < q.size(); ++n) {
                 uint32_t* w = &sec_dt[8 * n];
@@ -162,11 +235,14 @@ int prepare_fused(fd_handle* h) {
             }
             rc = upload(h, &m.dt_tab, dtab.data(), dtab.size());
             if (!rc) rc = upload(h, reinterpret_cast<uint32_t**>(&m.nodes_dt), sec_dt.data(), sec_dt.size());
+            if (!rc && shallow) rc = upload(h, &m.dt_heap, heap.data(), heap.size());
+            if (!rc && shallow) rc = upload(h, &m.dt_out, outv.data(), outv.size());
             if (rc) return rc;
             m.dt_mul = mul;
             m.dt_log2 = lg;
             m.dt_shift = 32 - lg;
             m.dt_small = 1;
+            m.dt_heap_on = shallow ? 1 : 0;
         }
     }
     return FD_OK;
@@ -222,8 +298,9 @@ int fd_destroy(fd_handle* h) {
     cudaFree(m.vocab_pool);
     cudaFree(m.idf);
     cudaFree(m.coef);
-    cudaFree(m.lr_nz);
-    cudaFree(m.used_nz);
+    cudaFree(m.filt);
+    cudaFree(m.dt_heap);
+    cudaFree(m.dt_out);
     cudaFree(m.nodes);
     cudaFree(m.nodes_s);
     cudaFree(m.nodes_dt);
@@ -253,6 +330,8 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
     Model& m = h->m;
     m.empty_is_stop = 0;
     m.drop_empty = m.empty_absent;
+    h->host_stop.clear();
+    h->fused_dirty = true;
     if (n_words == 0) {
         if (m.sw_tab) cudaFree(m.sw_tab);
         if (m.sw_words) cudaFree(m.sw_words);
@@ -263,7 +342,7 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
         m.sw_cap = 0;
         m.n_sw = 0;
         m.sw_perfect = 0;
-        return FD_OK;
+        return prepare_fused(h);
     }
     if (n_words > 2048) return set_err(h, FD_ERR_LIMIT, "at most 2048 stop words are supported (got %d)", n_words);
     // word records first (duplicates collapse), then a 2-choice cuckoo table over them: every word sits in one of
@@ -306,7 +385,7 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
     std::vector<uint32_t> tab;
     int cap = 0;
     m.sw_perfect = 0;
-    for (int lg = 11; lg <= 12 && !m.sw_perfect && wordsv.size() <= 400; ++lg) {
+    for (int lg = 11; lg <= 12 && !m.sw_perfect && !wordsv.empty() && wordsv.size() <= 400; ++lg) {
         std::vector<uint16_t> t16((size_t)1 << lg);
         uint64_t x = 0x9E3779B97F4A7C15ULL;
         for (int trial = 0; trial < (lg == 11 ? 60000 : 400000) && !m.sw_perfect; ++trial) {
@@ -365,7 +444,9 @@ int fd_set_stopwords(fd_handle* h, const uint8_t* words, const int32_t* offs, in
     if (rc) return rc;
     m.sw_cap = wordsv.empty() ? 0 : cap;
     m.n_sw = (int)wordsv.size();
-    return FD_OK;
+    if (wordsv.empty()) m.sw_perfect = 0;
+    h->host_stop = seen;
+    return prepare_fused(h);
 }
 
 int fd_hash_terms(const uint8_t* terms, const int32_t* offs, int32_t n, int32_t num_features, int32_t* out) {
@@ -378,13 +459,33 @@ int fd_hash_terms(const uint8_t* terms, const int32_t* offs, int32_t n, int32_t 
     return FD_OK;
 }
 
+// The IDF vector, the coefficients and the forest are indexed by feature: when the feature space changes they are
+// dropped (the compute calls answer FD_ERR_STATE until the IDF stage and the classifier are set again).
+static void drop_feature_space(fd_handle* h, int32_t new_num_features, bool meaning_changed) {
+    Model& m = h->m;
+    if (m.num_features == new_num_features && !meaning_changed) return;
+    if (m.idf) cudaFree(m.idf);
+    m.idf = nullptr;
+    h->host_idf.clear();
+    m.classifier = 0;
+    m.int_walk = 0;
+    m.dt_small = 0;
+    m.dt_heap_on = 0;
+    m.filt_on = 0;
+    h->filt_want = false;
+    h->host_seen.clear();
+    h->host_nodes.clear();
+}
+
 int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary) {
     if (!h || num_features <= 0) return set_err(h, FD_ERR_INVALID, "numFeatures must be > 0");
+    FD_CUDA(h, cudaSetDevice(h->device));
     Model& m = h->m;
+    drop_feature_space(h, num_features, !h->host_vocab.empty());  // (same size but hashed, not looked up: other features)
     m.num_features = num_features;
     m.binary = binary ? 1 : 0;
-    m.used_on = 0;    // bitmaps sized for another feature space are not consulted (set the classifier after the featuriser)
-    m.lr_sparse = 0;
+    h->host_vocab.clear();
+    h->fused_dirty = true;
     m.mod_pow2 = (num_features & (num_features - 1)) == 0;
     m.mod_magic = m.mod_pow2 ? 0u : (uint32_t)((1ULL << 32) / (uint64_t)num_features);
     m.mod_r32 = (uint32_t)((1ULL << 32) % (uint64_t)num_features);
@@ -398,7 +499,7 @@ int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary) {
     m.vocab_cap = 0;
     m.empty_absent = 0;
     m.drop_empty = m.empty_is_stop;
-    return FD_OK;
+    return prepare_fused(h);
 }
 
 int fd_set_vocabulary(fd_handle* h, const uint8_t* words, const int32_t* offs, int32_t n_words, int32_t binary) {
@@ -457,15 +558,17 @@ int fd_set_vocabulary(fd_handle* h, const uint8_t* words, const int32_t* offs, i
     if (!rc) rc = upload(h, &m.vocab_pool, pool.data(), pool.size());
     if (rc) return rc;
     m.vocab_cap = cap;
+    drop_feature_space(h, n_words, true);
     m.num_features = n_words;
     m.binary = binary ? 1 : 0;
-    m.used_on = 0;    // bitmaps sized for another feature space are not consulted (set the classifier after the featuriser)
-    m.lr_sparse = 0;
     m.mod_pow2 = 0;
     m.empty_absent = empty_id < 0;
     m.empty_idx = empty_id < 0 ? 0u : (uint32_t)empty_id;
     m.drop_empty = m.empty_is_stop || m.empty_absent;
-    return FD_OK;
+    h->host_vocab.assign((size_t)n_words, std::vector<uint8_t>());
+    for (int i = 0; i < n_words; ++i) h->host_vocab[(size_t)i].assign(words + offs[i], words + offs[i + 1]);
+    h->fused_dirty = true;
+    return prepare_fused(h);
 }
 
 int fd_set_idf(fd_handle* h, const double* idf, int32_t num_features) {
@@ -499,19 +602,18 @@ int fd_set_linear(fd_handle* h, const double* coef_dense, int32_t num_features, 
                 nz[(size_t)i >> 5] |= 1u << (i & 31);
                 ++kept;
             }
-        rc = upload(h, &h->m.lr_nz, nz.data(), nz.size());
-        if (rc) return rc;
+        h->host_seen = nz;
         h->m.lr_keep = (float)kept / (float)num_features;
-        h->m.lr_sparse = kept * 10 <= (size_t)num_features * 9;  // worth a bitmap probe per term from 10 % zeros
+        h->filt_want = kept * 10 <= (size_t)num_features * 9;  // worth a bitmap probe per term from 10 % zeros
     }
     h->m.intercept = intercept;
     // LogisticRegressionModel.raw2prediction: rawThreshold = log(t / (1 - t)), -inf at 0, +inf at 1
     h->m.raw_threshold = threshold <= 0.0 ? -INFINITY : (threshold >= 1.0 ? INFINITY : std::log(threshold / (1.0 - threshold)));
     h->m.classifier = 1;
     h->m.n_classes = 2;
-    h->m.int_walk = 0;
-    h->m.dt_small = 0;
-    return FD_OK;
+    h->host_nodes.clear();
+    h->fused_dirty = true;
+    return prepare_fused(h);
 }
 
 int fd_set_forest(fd_handle* h, int32_t kind, int32_t n_trees, const int32_t* tree_offsets, const int32_t* feature,
@@ -587,10 +689,12 @@ int fd_set_forest(fd_handle* h, int32_t kind, int32_t n_trees, const int32_t* tr
                 used[(size_t)nd.feat >> 5] |= 1u << (nd.feat & 31);
                 ++n_used;
             }
-        rc = upload(h, &m.used_nz, used.data(), used.size());
-        if (rc) return rc;
-        m.used_on = h->m.num_features > 0 && n_used * 2 <= (size_t)h->m.num_features;
+        h->host_seen = used;
+        h->filt_want = h->m.num_features > 0 && n_used * 2 <= (size_t)h->m.num_features;
     }
+    h->host_leaf2 = leaf2;
+    h->host_leafp = leafp;
+    h->host_root0 = roots[0];
     h->host_nodes = nodes;
     h->fused_dirty = true;
     m.kind = kind;

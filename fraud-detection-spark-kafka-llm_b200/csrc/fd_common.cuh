@@ -72,16 +72,16 @@ struct Model {
     // classifier
     int classifier = 0;  // 0 none, 1 linear, 2 forest
     double* coef = nullptr;
-    // LogisticRegression with exact-zero coefficients (L1 / elastic-net fits; 59 % of the shipped model's): a term whose
-    // coefficient is +-0.0 adds +-0.0 to the margin, which never changes a sum that starts at +0.0, so the fused kernel
-    // drops such terms before they reach the count table (bit i of lr_nz = coef[i] != 0).  lr_keep = fraction kept.
-    uint32_t* lr_nz = nullptr;
-    int lr_sparse = 0;
-    float lr_keep = 1.0f;
-    // Forests likewise only ever look at the features their nodes split on: bit i of used_nz = some node splits on
-    // feature i; every other term is dropped before the count table (fewer inserts, fewer overflowing dialogues).
-    uint32_t* used_nz = nullptr;
-    int used_on = 0;
+    // What the classifier can see.  A LogisticRegression term with an exact-zero coefficient adds +-0.0 to a sum that
+    // starts at +0.0 (L1 / elastic-net fits; 59 % of the shipped model's coefficients), and a forest only ever looks at
+    // the features its nodes split on: every other term is dropped before it reaches the count table.  The same bitmap
+    // makes the stop-word lookup unnecessary for almost every token: a stop word only matters when its bucket is one
+    // the classifier can see, so the fused kernels probe the stop-word table only for tokens whose bucket carries the
+    // second bit.  Word i of filt covers features 32 i .. 32 i + 31: x = "visible to the classifier",
+    // y = "visible AND some stop word maps to this feature" (rebuilt by prepare_fused from the host copies below).
+    uint2* filt = nullptr;
+    int filt_on = 0;         // consult filt (off when the classifier sees most features anyway)
+    float lr_keep = 1.0f;    // fraction of the features a sparse LogisticRegression keeps
     double intercept = 0.0, raw_threshold = 0.0;
     int kind = 0, n_trees = 0, n_classes = 2;
     Node* nodes = nullptr;
@@ -98,8 +98,15 @@ struct Model {
     int dt_small = 0;
     uint32_t dt_mul = 0;
     int dt_shift = 0, dt_log2 = 0;
-    uint32_t* dt_tab = nullptr;
+    uint32_t* dt_tab = nullptr;  // bit 31 of an entry: some stop word maps to this feature (probe the stop-word table)
     uint4* nodes_dt = nullptr;
+    // ... and when the tree is at most 5 levels deep the main kernel evaluates all of its <= 31 split nodes at once, one
+    // per lane, in heap order (root 0, children 2 i + 1 and 2 i + 2; a position below a leaf repeats "go left"), and
+    // walks the ballot: dt_heap[i] = {counter slot, count threshold}, dt_out[p] = the five result doubles
+    // (prediction, probability 0/1, rawPrediction 0/1) of the leaf reached at depth-5 position p (0..31).
+    int dt_heap_on = 0;
+    int2* dt_heap = nullptr;
+    double* dt_out = nullptr;
     int32_t* roots = nullptr;  // absolute root index per tree
     double2* leaf2 = nullptr;  // DT: raw class stats, RF: stats / total (0,0 when total == 0)
     double2* leaf_prob = nullptr;  // DT: stats / total, divided once on the host (IEEE division: same bits as on the device)
@@ -132,7 +139,16 @@ struct fd_handle {
     // host copies needed to (re)build nodes_s when the idf vector or the forest changes
     std::vector<fd::Node> host_nodes;
     std::vector<double> host_idf;
+    std::vector<double2> host_leaf2, host_leafp;     // per node: leaf statistics / probabilities (Model::leaf2, leaf_prob)
+    int host_root0 = 0;                              // node index of the first tree's root
+    bool filt_want = false;                          // the classifier sees few enough features for Model::filt to pay
+    std::vector<uint32_t> host_seen;                 // bitmap of the features the classifier can see (non-zero coefficient / split feature)
+    std::vector<std::vector<uint8_t>> host_stop;     // stop words as uploaded (lower-cased unless case sensitive), for the filt.y bits
+    std::vector<std::vector<uint8_t>> host_vocab;    // CountVectorizerModel vocabulary (empty: hashing trick)
     bool fused_dirty = false;
+    // launch configuration of the main kernel, cached per (instantiation, shared-memory size)
+    struct LaunchCfg { const void* fn; size_t smem; int occ; };
+    std::vector<LaunchCfg> launch_cfg;
 };
 
 namespace fd {

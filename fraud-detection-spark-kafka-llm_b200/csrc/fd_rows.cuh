@@ -78,11 +78,9 @@ struct RowArgs {
     double* raw;
 };
 
-template <int MODE>
-__device__ void row_epilogue(const RowArgs& a, double* scratch, unsigned long long* tab, int log2cap, long long row, int D,
-                             int lane);
-
 cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st);
+cudaError_t launch_main_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st);  // fd_main.cu
+void launch_pick_shape(fd_handle* h, const RowArgs& a, float keep, cudaStream_t st);
 cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st);
 cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, const unsigned long long* tmp,
                                 long long n_rows, long long* bsum, long long* rowptr, int32_t* out_idx, double* out_val,

@@ -129,10 +129,12 @@ def hash_terms(terms: Sequence[bytes], num_features: int) -> np.ndarray:
 
 
 def random_tree(rng: np.random.Generator, depth: int, features: np.ndarray, idf: Optional[np.ndarray], regression: bool = False,
-                full: bool = True) -> sf.TreeArrays:
+                full: bool = True, weights: Optional[np.ndarray] = None) -> sf.TreeArrays:
     """A random binary tree of the given depth in Spark's pre-order numbering.  Split features come from
-    `features` (buckets that actually occur), thresholds sit between the tf-idf values of 0..3 occurrences
-    so that both branches are taken.  Classification leaves carry random class counts."""
+    `features` (buckets that actually occur; drawn uniformly, or in proportion to `weights` -- e.g. their document
+    frequencies, as a trained tree prefers features that occur), thresholds sit between the tf-idf values of 0..3
+    occurrences so that both branches are taken.  Classification leaves carry random class counts."""
+    pw = None if weights is None else np.asarray(weights, dtype=np.float64) / float(np.sum(weights))
     feature, threshold, left, right, pred, stats = [], [], [], [], [], []
 
     def grow(d):
@@ -154,7 +156,7 @@ def random_tree(rng: np.random.Generator, depth: int, features: np.ndarray, idf:
             pred.append(float(np.argmax(c)))
             stats.append(list(c))
         if not leaf:
-            f = int(features[rng.integers(0, len(features))])
+            f = int(features[rng.integers(0, len(features)) if pw is None else rng.choice(len(features), p=pw)])
             w = 1.0 if idf is None else float(idf[f])
             feature[me] = f
             threshold[me] = w * (float(rng.integers(0, 3)) + 0.5)

@@ -28,8 +28,8 @@ def c2(fd):
     _, idx, _ = fd.PipelineModel(stages).featurize(fd.PackedText(pk.data, pk.offs[:ns + 1]), cleaned=False)
     df = torch.bincount(idx.long(), minlength=nf).cpu().numpy()
     idf = fd.IDF(inputCol="raw_features", outputCol="features").fit_from_doc_freq(df, ns)
-    top = synth.hash_terms(corpus.words[corpus.n_stop:corpus.n_stop + 12] + [b""], nf)  # frequent words: both branches taken
-    tree = synth.random_tree(np.random.default_rng(20261106), 5, top, idf.idf)
+    top = synth.hash_terms(corpus.words[corpus.n_stop:corpus.n_stop + 2000] + [b""], nf)  # the 2,000 most frequent buckets, as bench.py
+    tree = synth.random_tree(np.random.default_rng(20261106), 5, top, idf.idf, weights=df[top])  # drawn by document frequency: both branches taken
     model = fd.PipelineModel(stages + [idf, fd.DecisionTreeClassificationModel(tree, nf)])
     return model, pk
 

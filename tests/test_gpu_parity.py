@@ -264,6 +264,47 @@ def test_tree_walk_corner_cases(fd, kind, weights):
     assert len(np.unique(exp[2][:, 1])) > 3
 
 
+@pytest.mark.parametrize("kind", ["dt", "rf", "gbt", "lr"])
+@pytest.mark.parametrize("case_sensitive", [False, True])
+def test_classifier_features_that_stop_words_map_to(fd, kind, case_sensitive):
+    """The fused kernels skip the stop-word lookup for terms the classifier cannot see and probe it only for buckets
+    that both the classifier sees and a stop word maps to.  Here the classifier splits on (or weighs) exactly such
+    buckets: the buckets of 'the', 'a', 'of', 'to' next to those of ordinary words, with a stop-word list that also
+    holds a word longer than 12 bytes.  A removed stop word must not be counted; with a case-sensitive list of
+    capitalised words nothing matches the lower-cased tokens and everything is counted."""
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    nf = 1 << 12
+    rng = np.random.default_rng(41)
+    stop = ["the", "a", "of", "to", "and", "is", "i", "antidisestablishmentarianism"]
+    if case_sensitive:
+        stop = [w.capitalize() for w in stop] + ["hello"]
+    words = [b"the", b"a", b"of", b"to", b"hello", b"social", b"number", b"verify", b"antidisestablishmentarianism", b"q", b""]
+    feats = synth.hash_terms(words, nf)
+    idf = np.log(401.0 / (rng.integers(0, 400, size=nf) + 1.0))
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"),
+              fd.StopWordsRemover(inputCol="words", outputCol="filtered_words", stopWords=stop, caseSensitive=case_sensitive),
+              fd.HashingTF(inputCol="filtered_words", outputCol="raw_features", numFeatures=nf),
+              fd.IDFModel(idf, inputCol="raw_features", outputCol="features")]
+    if kind == "dt":
+        cl = fd.DecisionTreeClassificationModel(synth.random_tree(rng, 5, feats, idf), nf)
+    elif kind == "rf":
+        cl = fd.RandomForestClassificationModel([synth.random_tree(rng, 4, feats, idf, full=False) for _ in range(12)], nf)
+    elif kind == "gbt":
+        trees = [synth.random_tree(rng, 3, feats, idf, regression=True, full=False) for _ in range(9)]
+        cl = fd.GBTClassificationModel(trees, [1.0] + [0.1] * 8, nf)
+    else:
+        coef = np.zeros(nf)
+        coef[feats] = rng.normal(0.0, 1.0, size=len(feats))
+        cl = fd.LogisticRegressionModel(coef, -0.3)
+    model = fd.PipelineModel(stages + [cl])
+    rows = messy_texts(600, seed=21, max_tokens=90) + _long_rows()[:6]
+    exp = oracle_for(model).transform([t.encode() for t in rows])
+    _check_scores(model.transform(rows), exp)
+    rowptr, idx, val = model.featurize(rows)
+    _check_scores(model.score(rowptr, idx, val), exp)
+    assert len(np.unique(exp[2][:, 1])) > 3
+
+
 @pytest.mark.parametrize("kind,n_trees,depth", [("rf", 40, 7), ("gbt", 24, 5), ("dt", 1, 6)])
 def test_forests_in_the_large_batch_shape(fd, kind, n_trees, depth):
     """Batches of at least 65,536 short dialogues run the 256-slot-table shape of the kernel (16 warps per CTA); the
