@@ -243,6 +243,9 @@ int prepare_fused(fd_handle* h) {
             m.dt_shift = 32 - lg;
             m.dt_small = 1;
             m.dt_heap_on = shallow ? 1 : 0;
+            m.dt_stop = 0;
+            for (uint32_t e : dtab)
+                if (e != 0xFFFFFFFFu && (e >> 31)) m.dt_stop = 1;
         }
     }
     return FD_OK;

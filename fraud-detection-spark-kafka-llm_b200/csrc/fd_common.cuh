@@ -105,6 +105,7 @@ struct Model {
     // walks the ballot: dt_heap[i] = {counter slot, count threshold}, dt_out[p] = the five result doubles
     // (prediction, probability 0/1, rawPrediction 0/1) of the leaf reached at depth-5 position p (0..31).
     int dt_heap_on = 0;
+    int dt_stop = 0;           // some split feature is also the bucket of a stop word (bit 31 set somewhere in dt_tab)
     int2* dt_heap = nullptr;
     double* dt_out = nullptr;
     int32_t* roots = nullptr;  // absolute root index per tree

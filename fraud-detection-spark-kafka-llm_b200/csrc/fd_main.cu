@@ -24,6 +24,9 @@
 // Semantics restated from Spark 3.5.5; reference call sites:
 // utils/agent_api.py:143-144 (cleaning), fraud_detection_spark.py:50-53 (Tokenizer, StopWordsRemover, HashingTF/IDF
 // stages), utils/agent_api.py:158-167 (transform + result columns).
+#include <cstddef>
+#include <type_traits>
+
 #include "fd_rows_dev.cuh"
 
 namespace fd {
@@ -122,10 +125,47 @@ __device__ __noinline__ uint32_t fix_non_ascii(uint8_t* rb, int p0, uint32_t bit
     return add;
 }
 
+// ---- shared-memory accesses by 32-bit shared address.  The hot loops address the warp's buffers through a few base
+// addresses held in registers; going through generic pointers made the compiler rebuild the shared window base (three
+// uniform-datapath instructions) at every use.
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint4 lds_v4(uint32_t a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_u16(uint32_t a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void red_add_u32(uint32_t a, uint32_t v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ int bfind_u32(uint32_t x) {  // index of the highest set bit (x != 0)
+    int b;
+    asm("bfind.u32 %0, %1;" : "=r"(b) : "r"(x));
+    return b;
+}
+// rotate left by a constant as ONE funnel shift (written in PTX so that "multiply, then rotate" is not turned into
+// two multiplies and a LEA.HI)
+template <int R>
+__device__ __forceinline__ uint32_t rotl_c(uint32_t x) {
+    uint32_t y;
+    asm("shf.l.wrap.b32 %0, %1, %1, %2;" : "=r"(y) : "r"(x), "n"(R));
+    return y;
+}
+__device__ __forceinline__ uint32_t mmk(uint32_t k) { return rotl_c<15>(k * 0xcc9e2d51u) * 0x1b873593u; }
+
 // MODE: what happens to the counted terms (fd_rows.cuh); CLEAN: FD_FLAG_CLEAN; TL: log2 of the count-table slots and the
 // CTA shape (row_warps); DTS: small-decision-tree path (MODE_DT with Model::dt_heap_on, hashing trick) -- per-warp counters
-// instead of a count table, nothing is ever deferred for size.
-template <int MODE, bool CLEAN, int TL, bool DTS>
+// instead of a count table, nothing is ever deferred for size; 2 = some split feature is also a stop word's bucket;
+// POW2: HashingTF with a power-of-two numFeatures (bucket = hash & mask).
+template <int MODE, bool CLEAN, int TL, int DTS, bool POW2>
 __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(const RowArgs a, const int cta_bytes, const int warp_bytes) {
     constexpr int ROW_WARPS = row_warps(TL);
     constexpr uint32_t FULL = 0xFFFFFFFFu;
@@ -145,6 +185,13 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
     MainWarp& S = *reinterpret_cast<MainWarp*>(wmem);
     unsigned long long* stab = reinterpret_cast<unsigned long long*>(wmem + sizeof(MainWarp));  // !DTS: (count, bucket) slots
     uint32_t* cnt = reinterpret_cast<uint32_t*>(wmem + sizeof(MainWarp));                       // DTS: one counter per slot
+    // the same places as shared addresses
+    uint32_t lutA;  // (opaque to the compiler, so that it stays in a register instead of being rebuilt at every use)
+    asm volatile("mov.u32 %0, %1;" : "=r"(lutA) : "r"(smem_u32(smem_raw)));
+    const uint32_t dtkA = lutA + LUT_BYTES;
+    const uint32_t rawA = smem_u32(wmem);
+    const uint32_t tokA = rawA + (uint32_t)offsetof(MainWarp, tok);
+    const uint32_t cntA = rawA + (uint32_t)sizeof(MainWarp);
 
     if (threadIdx.x < 13) {
         const int n = threadIdx.x;
@@ -175,7 +222,6 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
 
     const uint8_t* text = a.text;
     const bool binary = m.binary != 0;
-    const bool pow2 = m.mod_pow2 && !m.vocab_cap;  // bucket = h & (numFeatures - 1)
     const uint32_t fmask = (uint32_t)(m.num_features - 1);
     unsigned long long* tab = stab;  // TL == 9: may move to the warp's wide table in global memory
     int TLOG2 = TL;
@@ -221,6 +267,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
 
     for (;;) {
         uint8_t* rb = S.raw[buf];
+        const uint32_t rbA = rawA + (uint32_t)buf * ROW_RAWBUF;
         if (cur_loaded) {
             if (buf == 0) {
                 mbar_wait(&S.mbar[0], phase0);
@@ -266,14 +313,15 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
         }
         int win_sp = __shfl_sync(FULL, incl, 31);
         {
-            uint16_t* tp = S.tok + 1 + incl - nsp;
-            uint32_t r = __brev(SP);  // separators from the top bit down
-            int pos = 32 * lane;      // buffer offset of the byte after the separator found last
-            while (r) {
-                const int d = __clz(r) + 1;
-                pos += d;
-                r = d < 32 ? r << d : 0u;
-                *tp++ = (uint16_t)pos;
+            // this lane's separators, highest first: entry [incl] down to [incl - nsp + 1] of the list
+            uint32_t ta = tokA + 2u * (uint32_t)incl;
+            uint32_t sp = SP;
+            const uint32_t p1 = 32u * (uint32_t)lane + 1u;
+            while (sp) {
+                const int b = bfind_u32(sp);
+                sts_u16(ta, p1 + (uint32_t)b);
+                ta -= 2u;
+                sp ^= 1u << b;
             }
         }
         const int my_ll = L ? (32 * lane + 31 - __clz(L)) : -1;
@@ -363,10 +411,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                 if (DTS) {
                     // (the empty token's bucket is a split feature only by accident; it is never a stop word)
                     const uint32_t fi = m.empty_idx, slot = (fi * m.dt_mul) >> m.dt_shift;
-                    if (lane == 0 && ((dtk[slot] ^ fi) & 0x7FFFFFFFu) == 0u) {
-                        if (binary) cnt[slot] = 1u;
-                        else atomicAdd(&cnt[slot], pend);
-                    }
+                    if (lane == 0 && ((dtk[slot] ^ fi) & 0x7FFFFFFFu) == 0u) atomicAdd(&cnt[slot], pend);
                 } else {
                     bool isnew = false;
                     const uint32_t fi = m.empty_idx;
@@ -378,7 +423,10 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
             pend = 0;
             row_letter = true;
         }
-        if (!big) {
+        // The loop body exists twice: for plain windows (token = the bytes between two separators) and for windows with
+        // dropped bytes (kept-byte analysis per token, byte-wise walk for tokens whose kept bytes are not one run).
+        auto pass_b = [&](auto plain_tag) {
+            constexpr bool PLAIN = decltype(plain_tag)::value;
             for (int t0 = 0; t0 < Tc; t0 += 32) {
                 if (!DTS && D + 32u > (3u << TLOG2) / 4u) {  // keep the table at most 3/4 full
                     const long long gw = (long long)blockIdx.x * ROW_WARPS + warp;
@@ -403,14 +451,14 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                 // ---- token extent and its kept-byte pattern
                 const int ti = t0 + lane;
                 const bool valid = ti < Tc;
-                const int tt = valid ? ti : 0;
-                int s = S.tok[tt];
-                const int e = (int)S.tok[tt + 1] - 1;
+                const uint32_t ta = tokA + 2u * (uint32_t)(valid ? ti : 0);
+                int s = (int)lds_u16(ta);
+                const int e = (int)lds_u16(ta + 2u) - 1;
                 const int len = e - s;
                 uint32_t n;      // kept bytes
                 int p0, nn;      // where the straight-line hash reads, and how many bytes (0: nothing)
                 bool empty, slow = false;
-                if (plain) {     // every byte between two separators is kept
+                if (PLAIN) {     // every byte between two separators is kept
                     n = (uint32_t)len;
                     p0 = s;
                     nn = len;
@@ -429,26 +477,27 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                 // ---- murmur3 of a contiguous token, first 12 bytes straight-line
                 uint32_t b0, b1, b2, h;
                 {
-                    const uint32_t* wp = reinterpret_cast<const uint32_t*>(rb + (p0 & ~3));
-                    const int sh8 = (p0 & 3) * 8;
-                    const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
-                    const uint4 mk = lut[min(nn, 12)];
+                    const uint32_t pa = rbA + (uint32_t)p0;
+                    const uint32_t wa = pa & ~3u;
+                    const uint32_t sh8 = pa << 3;  // (the funnel shift takes the amount modulo 32; the buffer is 16-byte aligned)
+                    const uint32_t w0 = lds_u32(wa), w1 = lds_u32(wa + 4u), w2 = lds_u32(wa + 8u), w3 = lds_u32(wa + 12u);
+                    const uint4 mk = lds_v4(lutA + 16u * (uint32_t)min(nn, 12));
                     b0 = __funnelshift_r(w0, w1, sh8) & mk.x;
                     b1 = __funnelshift_r(w1, w2, sh8) & mk.y;
                     b2 = __funnelshift_r(w2, w3, sh8) & mk.z;
-                    // a block past the token is all zero and mm_k(0) = 0, so "h ^= mm_k(block)" covers both the tail block
+                    // a block past the token is all zero and mmk(0) = 0, so "h ^= mmk(block)" covers both the tail block
                     // and the blocks beyond it: one select per block (full block -> rotate/multiply step)
-                    uint32_t t = 42u ^ mm_k(b0);
-                    h = nn >= 4 ? rotl32(t, 13) * 5u + 0xe6546b64u : t;
-                    t = h ^ mm_k(b1);
-                    h = nn >= 8 ? rotl32(t, 13) * 5u + 0xe6546b64u : t;
-                    t = h ^ mm_k(b2);
-                    h = nn >= 12 ? rotl32(t, 13) * 5u + 0xe6546b64u : t;
+                    uint32_t t = 42u ^ mmk(b0);
+                    h = nn >= 4 ? rotl_c<13>(t) * 5u + 0xe6546b64u : t;
+                    t = h ^ mmk(b1);
+                    h = nn >= 8 ? rotl_c<13>(t) * 5u + 0xe6546b64u : t;
+                    t = h ^ mmk(b2);
+                    h = nn >= 12 ? rotl_c<13>(t) * 5u + 0xe6546b64u : t;
                     if (__any_sync(FULL, nn > 12)) {
                         if (nn > 12) {
                             uint32_t prev = w3;
                             for (int i = 3; nn > 4 * i; ++i) {
-                                const uint32_t nxt = wp[i + 1];
+                                const uint32_t nxt = lds_u32(wa + 4u * (uint32_t)(i + 1));
                                 const uint32_t k = __funnelshift_r(prev, nxt, sh8);
                                 prev = nxt;
                                 const int r = nn - 4 * i;
@@ -458,7 +507,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                     }
                     h = mm_fmix(h, (uint32_t)nn);
                 }
-                if (!plain && __any_sync(FULL, slow)) {
+                if (!PLAIN && __any_sync(FULL, slow)) {
                     if (slow) {  // kept bytes are not contiguous (or the token is longer than 32 bytes): byte-wise walk
                         HashState hs;
                         hs.reset();
@@ -481,7 +530,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                 }
                 // ---- term index
                 uint32_t fi;
-                if (pow2) {
+                if (POW2) {
                     fi = h & fmask;  // (the empty token hashes to murmur3("") by itself: nn = 0)
                 } else if (!m.vocab_cap) {
                     fi = empty ? m.empty_idx : feature_index(h, m);
@@ -491,17 +540,15 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                     fi = ins ? fi : 0u;
                 }
                 if (DTS) {
-                    // small decision tree: bucket -> counter slot -> one compare -> one atomic; nothing is ever "new"
-                    const uint32_t slot = (fi * m.dt_mul) >> m.dt_shift;
-                    const uint32_t key = dtk[slot];
+                    // small decision tree: bucket -> counter slot -> one compare -> one shared-memory add; nothing is ever "new"
+                    // (a binary HashingTF counts too: the end of the dialogue clamps the counts to 1)
+                    const uint32_t slot4 = ((fi * m.dt_mul) >> m.dt_shift) * 4u;
+                    const uint32_t key = lds_u32(dtkA + slot4);
                     bool hit = ins && ((key ^ fi) & 0x7FFFFFFFu) == 0u;
-                    if (__any_sync(FULL, hit && (int)key < 0)) {  // a stop word maps to this split feature: is the token one?
+                    if (DTS == 2 && __any_sync(FULL, hit && (int)key < 0)) {  // a stop word maps to this split feature: is the token one?
                         if (hit && (int)key < 0 && !empty) hit = !stop_probe(m, m.sw_tab, m.sw_words, h, n, b0, b1, b2, rb, S.lmask, s, e, true);
                     }
-                    if (hit) {
-                        if (binary) cnt[slot] = 1u;
-                        else atomicAdd(&cnt[slot], 1u);
-                    }
+                    if (hit) red_add_u32(cntA + slot4, 1u);
                 } else {
                     if (MODE != MODE_CSR && m.filt_on) {
                         const uint2 fw = __ldg(&m.filt[fi >> 5]);
@@ -522,6 +569,10 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                     D += __popc(__ballot_sync(FULL, isnew));
                 }
             }
+        };
+        if (!big) {
+            if (plain) pass_b(std::true_type{});
+            else pass_b(std::false_type{});
         }
         __syncwarp();
 
@@ -558,12 +609,15 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                 }
             } else if (DTS) {
                 // every split node at once: lane i holds heap node i; bit i of the ballot = "go right at node i"
-                const uint32_t bits = __ballot_sync(FULL, (int)cnt[hn.x] > hn.y);
+                const uint32_t ca = cntA + 4u * (uint32_t)hn.x;
+                uint32_t c = lds_u32(ca);
+                if (binary) c = min(c, 1u);
+                const uint32_t bits = __ballot_sync(FULL, (int)c > hn.y);
                 int p = 0;
 #pragma unroll
                 for (int d = 0; d < 5; ++d) p = 2 * p + 1 + (int)((bits >> p) & 1u);
                 if (lane < 5) outp[(long long)row * ostride] = dto[(p - 31) * 5 + lane];
-                cnt[hn.x] = 0u;  // (only split-feature counters are ever touched; each is some lane's)
+                sts_u32(ca, 0u);  // (only split-feature counters are ever touched; each is some lane's)
             } else if (TL == 8 || tab == stab) {
                 row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), reinterpret_cast<double*>(rb), true, stab, TL, row, (int)D, lane);
             } else {
@@ -604,13 +658,13 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
 // ------------------------------------------------------------------------------------------------
 // launcher
 // ------------------------------------------------------------------------------------------------
-template <int MODE, bool CLEAN, int TL, bool DTS>
+template <int MODE, bool CLEAN, int TL, int DTS, bool POW2>
 static cudaError_t launch_k(fd_handle* h, const RowArgs& a, cudaStream_t st) {
     constexpr int NW = row_warps(TL);
     const size_t cta_bytes = LUT_BYTES + (DTS ? (((size_t)4 << a.m.dt_log2) + 160 * 8) : ((a.m.sw_smem_bytes() + 15) & ~(size_t)15));
     const size_t warp_bytes = sizeof(MainWarp) + (DTS ? ((size_t)4 << a.m.dt_log2) : ((size_t)8 << TL));
     const size_t smem = cta_bytes + (size_t)NW * warp_bytes;
-    auto kern = k_main<MODE, CLEAN, TL, DTS>;
+    auto kern = k_main<MODE, CLEAN, TL, DTS, POW2>;
     // shared-memory opt-in and occupancy are looked up once per (kernel, size) and kept in the handle
     int occ = 0;
     for (const auto& c : h->launch_cfg)
@@ -630,12 +684,12 @@ static cudaError_t launch_k(fd_handle* h, const RowArgs& a, cudaStream_t st) {
     return cudaGetLastError();
 }
 
-template <int MODE, bool CLEAN>
+template <int MODE, bool CLEAN, bool POW2>
 static cudaError_t launch_shapes(fd_handle* h, const RowArgs& a0, cudaStream_t st) {
     RowArgs a = a0;
     if (MODE == MODE_DT && a.m.dt_small && a.m.dt_heap_on && !a.m.vocab_cap) {
         a.pick_shape = 0;  // counters, not a table: one shape (16 warps per CTA) whatever the batch
-        return launch_k<MODE_DT, CLEAN, 8, true>(h, a, st);
+        return a.m.dt_stop ? launch_k<MODE_DT, CLEAN, 8, 2, POW2>(h, a, st) : launch_k<MODE_DT, CLEAN, 8, 1, POW2>(h, a, st);
     }
     a.m.dt_small = 0;  // (the generic path below keeps a full count table; the wide-table kernels see the caller's model)
     cudaError_t e;
@@ -644,15 +698,18 @@ static cudaError_t launch_shapes(fd_handle* h, const RowArgs& a0, cudaStream_t s
         // that was not picked exits at once
         a.pick_shape = 1;
         launch_pick_shape(h, a, (MODE == MODE_LINEAR && a.m.filt_on) ? a.m.lr_keep : 1.0f, st);
-        e = launch_k<MODE, CLEAN, 8, false>(h, a, st);
+        e = launch_k<MODE, CLEAN, 8, 0, POW2>(h, a, st);
         if (e != cudaSuccess) return e;
     }
-    return launch_k<MODE, CLEAN, 9, false>(h, a, st);
+    return launch_k<MODE, CLEAN, 9, 0, POW2>(h, a, st);
 }
 
 cudaError_t launch_main_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st) {
     const bool c = (a.flags & FD_FLAG_CLEAN) != 0;
-#define FD_DISPATCH(M) return c ? launch_shapes<M, true>(h, a, st) : launch_shapes<M, false>(h, a, st)
+    const bool p2 = a.m.mod_pow2 && !a.m.vocab_cap;
+#define FD_DISPATCH(M)                                                                                                 \
+    return c ? (p2 ? launch_shapes<M, true, true>(h, a, st) : launch_shapes<M, true, false>(h, a, st))                 \
+             : (p2 ? launch_shapes<M, false, true>(h, a, st) : launch_shapes<M, false, false>(h, a, st))
     switch (mode) {
         case MODE_CSR: FD_DISPATCH(MODE_CSR);
         case MODE_LINEAR: FD_DISPATCH(MODE_LINEAR);
