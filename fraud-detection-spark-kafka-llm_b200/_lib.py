@@ -38,6 +38,8 @@ SIGNATURES = {
     "fd_status": (C.c_int, [_p, _p]),
     "fd_transform_host": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _p]),
     "fd_transform_noalloc": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _p, _p, _p]),
+    "fd_workspace_bytes": (_i64, [_p, _i64]),
+    "fd_reserve": (C.c_int, [_p, _i64]),
     "fd_launch_count": (_i64, [_p]),
     "fd_bin_csr": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p, _p]),
     "fd_rf_histogram": (C.c_int, [_p, _p, _p, _p, _p, _i64, _i32, _p, _p, _p, _i32, _p, _p, _i32, _p, _p]),
@@ -66,7 +68,8 @@ def load_library():
     lib = C.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
         if not hasattr(lib, name):
-            continue  # exported-symbol coverage is asserted by tests/test_abi.py
+            raise RuntimeError(f"{LIB_PATH} does not export {name}: it was built from another version of the sources; "
+                               "rebuild it with `python __graft_entry__.py`")
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args

@@ -29,11 +29,14 @@ int cuda_fail(fd_handle* h, cudaError_t e, const char* what) {
     return set_err(h, FD_ERR_CUDA, "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
 }
 
-// grow the handle-owned workspace (contents are lost when it moves)
+// grow the handle-owned workspace (contents are lost when it moves, except the sticky device-side status, which is
+// carried over: an earlier asynchronous call may have reported FD_ERR_LIMIT there and nobody has read it yet)
 int ensure_ws(fd_handle* h, size_t bytes) {
     if (bytes <= h->ws_bytes) return FD_OK;
+    int carried = FD_OK;
     if (h->ws) {
         FD_CUDA(h, cudaDeviceSynchronize());
+        FD_CUDA(h, cudaMemcpy(&carried, &reinterpret_cast<Ctrl*>(h->ws)->status, sizeof(int), cudaMemcpyDeviceToHost));
         FD_CUDA(h, cudaFree(h->ws));
         h->ws = nullptr;
         h->ws_bytes = 0;
@@ -43,6 +46,8 @@ int ensure_ws(fd_handle* h, size_t bytes) {
     h->ws_bytes = bytes;
     h->feat_rows = -1;
     FD_CUDA(h, cudaMemset(h->ws, 0, 256));
+    if (carried != FD_OK)
+        FD_CUDA(h, cudaMemcpy(&reinterpret_cast<Ctrl*>(h->ws)->status, &carried, sizeof(int), cudaMemcpyHostToDevice));
     return FD_OK;
 }
 

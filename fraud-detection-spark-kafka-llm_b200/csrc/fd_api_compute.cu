@@ -50,15 +50,27 @@ static int read_ctrl(fd_handle* h, const Ctrl* dev, Ctrl* out, cudaStream_t st) 
     return FD_OK;
 }
 
+// featurize workspace: [slot fixed][row_nnz i32][row_tmpoff i64][bsum i64][tmp u64]
+struct FeatLayout {
+    size_t off_nnz, off_tmpoff, off_bsum, off_tmp, total;
+};
+static FeatLayout feat_layout(int64_t n_rows, int64_t tmp_cap) {
+    FeatLayout L;
+    const size_t nb = (size_t)((n_rows + 1023) / 1024);
+    L.off_nnz = slot_bytes(n_rows);
+    L.off_tmpoff = align_up(L.off_nnz + (size_t)n_rows * 4, 256);
+    L.off_bsum = align_up(L.off_tmpoff + (size_t)n_rows * 8, 256);
+    L.off_tmp = align_up(L.off_bsum + (nb + 1) * 8, 256);
+    L.total = L.off_tmp + (size_t)tmp_cap * 8;
+    return L;
+}
+// staging entries fd_featurize_begin starts with (it re-runs with the exact size when a batch needs more)
+static int64_t feat_guess(int64_t n_rows) { return std::max<int64_t>(1 << 20, n_rows * 96); }
+
 static int run_featurize_pass(fd_handle* h, const uint8_t* text, const int64_t* offs, int64_t n_rows, uint32_t flags,
                               int64_t tmp_cap, cudaStream_t st, Ctrl* result) {
-    // workspace: [slot fixed][row_nnz i32][row_tmpoff i64][bsum i64][tmp u64]
-    const size_t nb = (size_t)((n_rows + 1023) / 1024);
-    const size_t off_nnz = slot_bytes(n_rows);
-    const size_t off_tmpoff = align_up(off_nnz + (size_t)n_rows * 4, 256);
-    const size_t off_bsum = align_up(off_tmpoff + (size_t)n_rows * 8, 256);
-    const size_t off_tmp = align_up(off_bsum + (nb + 1) * 8, 256);
-    const size_t total = off_tmp + (size_t)tmp_cap * 8;
+    const FeatLayout L = feat_layout(n_rows, tmp_cap);
+    const size_t off_nnz = L.off_nnz, off_tmpoff = L.off_tmpoff, off_bsum = L.off_bsum, off_tmp = L.off_tmp, total = L.total;
     int rc = ensure_ws(h, total);
     if (rc) return rc;
     h->off_nnz = off_nnz;
@@ -105,7 +117,7 @@ int fd_featurize_begin(fd_handle* h, const uint8_t* text_dev, const int64_t* off
     }
     // staging capacity: total bytes are not known on the host, start from a per-dialogue guess and
     // re-run with the exact size if the kernel reports an overflow
-    int64_t cap = std::max<int64_t>(h->tmp_cap, std::max<int64_t>(1 << 20, n_rows * 96));
+    int64_t cap = std::max<int64_t>(h->tmp_cap, feat_guess(n_rows));
     Ctrl c;
     rc = run_featurize_pass(h, text_dev, offs_dev, n_rows, flags, cap, st, &c);
     if (rc) return rc;
@@ -190,6 +202,7 @@ int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev,
     cudaStream_t st = (cudaStream_t)stream;
     rc = ensure_ws(h, slot_bytes(n_rows));
     if (rc) return rc;
+    h->feat_rows = -1;  // (the scratch slot overlaps the staging arrays of an unfinished fd_featurize_begin)
     RowArgs a;
     memset(&a, 0, sizeof(a));
     a.text = text_dev;
@@ -219,6 +232,7 @@ int fd_vocab_count(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_de
     cudaStream_t st = (cudaStream_t)stream;
     int rc = ensure_ws(h, slot_bytes(n_rows));
     if (rc) return rc;
+    h->feat_rows = -1;  // (as in fd_transform)
     RowArgs a;
     memset(&a, 0, sizeof(a));
     a.text = text_dev;
@@ -239,6 +253,17 @@ int fd_vocab_count(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_de
     FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, CTRL_CLEAR_BYTES, st));
     FD_CUDA(h, launch_rows(h, MODE_FIT, a, st));
     return FD_OK;
+}
+
+int64_t fd_workspace_bytes(fd_handle* h, int64_t n_rows) {
+    if (!h || n_rows < 0) return FD_ERR_INVALID;
+    return (int64_t)std::max(slot_bytes(n_rows), feat_layout(n_rows, std::max<int64_t>(h->tmp_cap, feat_guess(n_rows))).total);
+}
+
+int fd_reserve(fd_handle* h, int64_t n_rows) {
+    if (!h || n_rows < 0) return set_err(h, FD_ERR_INVALID, "n_rows < 0");
+    FD_CUDA(h, cudaSetDevice(h->device));
+    return ensure_ws(h, (size_t)fd_workspace_bytes(h, n_rows));
 }
 
 int fd_status(fd_handle* h, void* stream) {

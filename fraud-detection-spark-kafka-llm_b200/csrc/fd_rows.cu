@@ -641,19 +641,100 @@ __global__ void k_scan_rowptr(const int32_t* __restrict__ nnz, long long n, cons
     if (i == n - 1) rowptr[n] = bsum[blockIdx.x] + sh[threadIdx.x];
 }
 
-__global__ void k_gather_csr(const unsigned long long* __restrict__ tmp, const long long* __restrict__ tmpoff,
-                             const long long* __restrict__ rowptr, long long n_rows, const double* __restrict__ idf,
-                             int32_t* __restrict__ out_idx, double* __restrict__ out_val) {
+// One dialogue's staged (count, bucket) entries -> its CSR row, ascending by bucket.  Up to 512 entries with buckets below
+// 2^23 are ordered in REGISTERS: the entries are read coalesced into shared memory as packed (bucket << 9 | position) keys
+// plus their counts, each lane then takes K consecutive keys, a bitonic network orders them (one shuffle per compare-exchange
+// across lanes), and the ordered keys go back through shared memory so that the row is written coalesced.
+constexpr int GATHER_WARPS = 8;
+template <int K>
+__device__ __forceinline__ void gather_sorted_k(const unsigned long long* __restrict__ src, int n, uint32_t* keys, uint32_t* cnts, int lane,
+                                                const double* __restrict__ idf, int32_t* __restrict__ oi, double* __restrict__ ov) {
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        const int e = r * 32 + lane;
+        uint32_t key = 0xFFFFFFFFu;
+        if (e < n) {
+            const unsigned long long x = src[e];
+            key = ((uint32_t)(x >> 32) << 9) | (uint32_t)e;
+            cnts[e] = (uint32_t)x;
+        }
+        keys[e] = key;
+    }
+    __syncwarp();
+    uint32_t v[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) v[r] = keys[lane * K + r];
+    __syncwarp();
+    bitonic_regs<K>(v, lane);
+#pragma unroll
+    for (int r = 0; r < K; ++r) keys[lane * K + r] = v[r];
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        const int e = r * 32 + lane;
+        if (e < n) {
+            const uint32_t key = keys[e];
+            const uint32_t idx = key >> 9;
+            const double c = (double)cnts[key & 511u];
+            oi[e] = (int32_t)idx;
+            ov[e] = idf ? __dmul_rn(c, __ldg(idf + idx)) : c;
+        }
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(32 * GATHER_WARPS, 4) k_gather_csr(unsigned long long* __restrict__ tmp, const long long* __restrict__ tmpoff,
+                                                                     const long long* __restrict__ rowptr, long long n_rows,
+                                                                     const double* __restrict__ idf, int small_keys,
+                                                                     int32_t* __restrict__ out_idx, double* __restrict__ out_val) {
+    __shared__ uint32_t key_sh[GATHER_WARPS][512];
+    __shared__ uint32_t cnt_sh[GATHER_WARPS][512];
     const int lane = threadIdx.x & 31;
-    const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
-    for (long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n_rows; r += nwarps) {
-        const long long o = rowptr[r], n = rowptr[r + 1] - o, t = tmpoff[r];
-        for (long long i = lane; i < n; i += 32) {
-            const unsigned long long e = tmp[t + i];
+    uint32_t* keys = key_sh[threadIdx.x >> 5];
+    uint32_t* cnts = cnt_sh[threadIdx.x >> 5];
+    const long long nwarps = (long long)gridDim.x * GATHER_WARPS;
+    for (long long r = (long long)blockIdx.x * GATHER_WARPS + (threadIdx.x >> 5); r < n_rows; r += nwarps) {
+        const long long o = rowptr[r], nl = rowptr[r + 1] - o;
+        unsigned long long* src = tmp + tmpoff[r];
+        int32_t* oi = out_idx + o;
+        double* ov = out_val + o;
+        if (small_keys && nl <= 512) {
+            const int n = (int)nl;
+            if (n <= 32) gather_sorted_k<1>(src, n, keys, cnts, lane, idf, oi, ov);
+            else if (n <= 64) gather_sorted_k<2>(src, n, keys, cnts, lane, idf, oi, ov);
+            else if (n <= 128) gather_sorted_k<4>(src, n, keys, cnts, lane, idf, oi, ov);
+            else if (n <= 256) gather_sorted_k<8>(src, n, keys, cnts, lane, idf, oi, ov);
+            else gather_sorted_k<16>(src, n, keys, cnts, lane, idf, oi, ov);
+            continue;
+        }
+        // long rows (or buckets of 2^23 and more): the 64-bit entries (bucket in the high word) are sorted in place in the
+        // staging buffer.  Normalised bitonic network -- every comparator ascending, the first step of a merge pairs i with
+        // its mirror i ^ (k - 1) -- so the positions from n up to the next power of two act as +infinity and are skipped.
+        long long P = 1;
+        while (P < nl) P <<= 1;
+        for (long long k = 2; k <= P; k <<= 1) {
+            for (long long j = k >> 1; j > 0; j >>= 1) {
+                const bool mirror = j == (k >> 1);
+                for (long long c = lane; c < (P >> 1); c += 32) {
+                    const long long i = ((c & ~(j - 1)) << 1) | (c & (j - 1));
+                    const long long q = mirror ? (i ^ (k - 1)) : (i | j);
+                    if (q < nl) {
+                        const unsigned long long x = src[i], y = src[q];
+                        if (x > y) {
+                            src[i] = y;
+                            src[q] = x;
+                        }
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        for (long long i = lane; i < nl; i += 32) {
+            const unsigned long long e = src[i];
             const uint32_t idx = (uint32_t)(e >> 32);
             const double c = (double)(uint32_t)e;
-            out_idx[o + i] = (int32_t)idx;
-            out_val[o + i] = idf ? __dmul_rn(c, __ldg(idf + idx)) : c;
+            oi[i] = (int32_t)idx;
+            ov[i] = idf ? __dmul_rn(c, __ldg(idf + idx)) : c;
         }
     }
 }
@@ -753,7 +834,7 @@ cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t s
     return launch_rows_workers(h, mode, a, MED_CTAS, BIG_WORKERS, st);
 }
 
-cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, const unsigned long long* tmp,
+cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, unsigned long long* tmp,
                                 long long n_rows, long long* bsum, long long* rowptr, int32_t* out_idx, double* out_val,
                                 bool scan_only, cudaStream_t st) {
     const int nb = (int)((n_rows + SCAN_BLOCK - 1) / SCAN_BLOCK);
@@ -764,9 +845,10 @@ cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long lon
         return cudaGetLastError();
     }
     k_scan_rowptr<<<nb, SCAN_BLOCK, 0, st>>>(nnz, n_rows, bsum, rowptr);
-    long long g = (n_rows + 7) / 8;
-    if (g > (long long)h->sm_count * 16) g = (long long)h->sm_count * 16;
-    k_gather_csr<<<(unsigned)g, 256, 0, st>>>(tmp, tmpoff, rowptr, n_rows, h->m.idf, out_idx, out_val);
+    long long g = (n_rows + GATHER_WARPS - 1) / GATHER_WARPS;
+    if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
+    k_gather_csr<<<(unsigned)g, 32 * GATHER_WARPS, 0, st>>>(tmp, tmpoff, rowptr, n_rows, h->m.idf, h->m.num_features <= (1 << 23) ? 1 : 0, out_idx,
+                                                       out_val);
     h->launches += 2;
     return cudaGetLastError();
 }

@@ -525,14 +525,23 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, double* scratch2
     const uint16_t* perm = nullptr;
     const bool small_keys = m.num_features <= (1 << 23);
     if (MODE == MODE_CSR) {
-        D = compact_and_sort(tab, log2cap, lane, small_keys, perm_buf, &perm);
+        // The table's entries go to the staging buffer in slot order, unsorted: the gather kernel (k_gather_csr) orders each
+        // dialogue's entries by bucket while it forms the values.  D = the number of occupied slots (counted at insertion).
         unsigned long long pos = 0;
         if (lane == 0) pos = atomicAdd(&a.ctrl->tmp_cursor, (unsigned long long)D);
         pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
-        if ((long long)(pos + D) <= a.tmp_cap) {
-            for (int i = lane; i < D; i += 32) a.tmp[pos + i] = tab[perm ? perm[i] : i];
-        } else if (lane == 0) {
-            a.ctrl->tmp_overflow = 1u;
+        const bool fits = (long long)(pos + D) <= a.tmp_cap;
+        if (!fits && lane == 0) a.ctrl->tmp_overflow = 1u;
+        unsigned long long* dst = a.tmp + pos;
+        const int cap = 1 << log2cap;
+        const uint32_t below = (1u << lane) - 1u;
+        uint32_t w = 0;
+        for (int base = 0; base < cap; base += 32) {
+            const unsigned long long e = tab[base + lane];
+            const bool v = (uint32_t)(e >> 32) != EMPTY_KEY;
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, v);
+            if (v && fits) dst[w + __popc(bal & below)] = e;
+            w += __popc(bal);
         }
         if (lane == 0) {
             a.row_nnz[row] = D;

@@ -359,7 +359,8 @@ class _TreeEnsembleModel(ClassificationModel):
     @property
     def featureImportances(self) -> np.ndarray:
         """``TreeEnsembleModel.featureImportances`` (reference fraud_detection_spark.py:233, 241): per tree
-        sum of gain x node instance count per split feature, normalised per tree, averaged, normalised."""
+        sum of gain x node instance count per split feature, normalised per tree (not for GBT, whose
+        ``perTreeNormalization`` is false in Spark), summed over the trees, normalised."""
         total = np.zeros(self.numFeatures, dtype=np.float64)
         for t in self.trees:
             imp = np.zeros(self.numFeatures, dtype=np.float64)
@@ -368,7 +369,9 @@ class _TreeEnsembleModel(ClassificationModel):
                 if t.feature[n] >= 0:
                     imp[t.feature[n]] += t.gain[n] * cnt[n]
             s = imp.sum()
-            if s > 0:
+            if self.kind == "gbt":
+                total += imp
+            elif s > 0:
                 total += imp / s
         s = total.sum()
         return total / s if s > 0 else total

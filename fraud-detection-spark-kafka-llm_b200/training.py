@@ -278,11 +278,23 @@ def features_per_node(strategy: str, n_trees: int, n_features: int) -> int:
         return max(1, int(math.ceil(math.log2(n_features))))
     if s == "onethird":
         return int(math.ceil(n_features / 3.0))
+    # DecisionTreeMetadata's order: an integer N > 0 means min(N, numFeatures) features; otherwise a fraction in (0, 1]
+    # means ceil(fraction * numFeatures); anything else is rejected ("1" is one feature, "1.0" is all of them)
+    try:
+        n = int(s)
+    except ValueError:
+        n = None
+    if n is not None:
+        if n <= 0:
+            raise ValueError(f"unsupported featureSubsetStrategy '{strategy}': an integer must be > 0")
+        return min(n, n_features)
     try:
         x = float(s)
     except ValueError:
         raise ValueError(f"unsupported featureSubsetStrategy '{strategy}'")
-    return max(1, int(x)) if x >= 1.0 and x == int(x) else int(math.ceil(x * n_features))
+    if not (0.0 < x <= 1.0):
+        raise ValueError(f"unsupported featureSubsetStrategy '{strategy}': a fraction must be in (0, 1]")
+    return int(math.ceil(x * n_features))
 
 
 def default_subset_fn(seed: int, n_features: int, k: int) -> Callable[[int, int], np.ndarray]:

@@ -63,9 +63,11 @@ int fd_version(void);
 
 /* ---- model upload (host pointers, synchronous) ---------------------------------------------- */
 /* Order: featuriser first (stop words, then HashingTF or the vocabulary), IDF, classifier last -- as the stages of the
- * saved pipeline come.  The classifier upload derives per-feature tables (quantised thresholds, the bitmaps of features the
- * model can see) from the feature space and the IDF vector in force; changing the featuriser afterwards switches those
- * bitmaps off until the classifier is set again. */
+ * saved pipeline come.  The IDF vector, the coefficients and the forest are indexed by feature, and the uploads derive
+ * per-feature tables from them (quantised thresholds, the bitmap of features the classifier can see and which of those a
+ * stop word maps to): a call that changes the feature space (fd_set_hashing with another numFeatures, any
+ * fd_set_vocabulary, or a switch between the two) DROPS the IDF vector and the classifier -- fd_transform / fd_score then
+ * answer FD_ERR_STATE until they are set again.  Changing only the stop words or the binary flag keeps them. */
 /* StopWordsRemover params (stages/1_StopWordsRemover_8c0b00b256b3/metadata/part-00000:1).
  * words = UTF-8 bytes back to back, offs = int32[n_words+1].  With case_sensitive == 0 ASCII
  * letters of the list are folded to lower case (the host folds non-ASCII ones before the call). */
@@ -162,6 +164,15 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
 int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev, int64_t n_rows,
                          uint32_t flags, double* out_pred_dev, double* out_prob_dev, double* out_raw_dev,
                          int32_t* out_status_dev, void* stream);
+/* The handle owns one device workspace (control block, deferred-dialogue list, wide count tables, CSR staging) that
+ * grows on demand: a compute call whose batch outgrows it SYNCHRONISES THE DEVICE, frees and reallocates it (cudaFree +
+ * cudaMalloc) before it enqueues anything.  fd_workspace_bytes says how many bytes a batch of n_rows dialogues needs
+ * (fd_transform and fd_featurize with its default staging estimate; the fixed part is about 204 MB), fd_reserve grows
+ * the workspace to that size now, so that later calls of up to n_rows dialogues neither allocate nor synchronise
+ * (fd_featurize on text with more than 96 distinct terms per dialogue on average still re-sizes its staging once).
+ * No counterpart in the reference: Spark sizes its executors' memory through spark.executor.memory. */
+int64_t fd_workspace_bytes(fd_handle* h, int64_t n_rows);
+int fd_reserve(fd_handle* h, int64_t n_rows);
 /* Number of kernel launches the handle has issued since creation (bench.py's gpu_launches). */
 int64_t fd_launch_count(fd_handle* h);
 

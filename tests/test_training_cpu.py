@@ -75,6 +75,15 @@ def test_features_per_node():
     assert training.features_per_node("auto", 100, 262144) == 512
     assert training.features_per_node("sqrt", 1, 10000) == 100
     assert training.features_per_node("log2", 5, 1024) == 10
+    # numeric strategies, in DecisionTreeMetadata's order: integer first (clamped), then a fraction in (0, 1]
+    assert training.features_per_node("1", 5, 1000) == 1
+    assert training.features_per_node("1.0", 5, 1000) == 1000
+    assert training.features_per_node("5000", 5, 1000) == 1000
+    assert training.features_per_node("0.25", 5, 1001) == 251
+    import pytest
+    for bad in ("0", "-3", "1.5", "0.0", "half"):
+        with pytest.raises(ValueError):
+            training.features_per_node(bad, 5, 1000)
 
 
 def _worker(rank, world, port, out):
