@@ -683,21 +683,127 @@ __device__ __forceinline__ void gather_sorted_k(const unsigned long long* __rest
     __syncwarp();
 }
 
+// Hashed buckets are spread evenly over [0, numFeatures), so a COUNTING SORT orders a dialogue's entries in a few dozen
+// instructions: bin = the bucket's top bits (256 bins, monotone in the bucket), a shared-memory atomic gives every entry its
+// arrival rank inside its bin, a scan turns the bin sizes into start positions, and entries that share a bin (a handful per
+// dialogue) are ordered by counting the bin's smaller keys.  bin_mul = floor(2^40 / numFeatures), 0 when numFeatures <= 256
+// (bin = bucket).  
+template <int K>
+__device__ __forceinline__ void gather_counted_k(const unsigned long long* __restrict__ src, int n, uint32_t* keys, uint32_t* fkeys,
+                                                 uint32_t* cnts, uint32_t* bins, uint32_t bin_mul, int lane, const double* __restrict__ idf,
+                                                 int32_t* __restrict__ oi, double* __restrict__ ov) {
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    reinterpret_cast<uint4*>(bins)[2 * lane] = z;
+    reinterpret_cast<uint4*>(bins)[2 * lane + 1] = z;
+    __syncwarp();
+    uint32_t key[K], rb[K], cn[K];  // rb = arrival rank << 8 | bin
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        const int e = r * 32 + lane;
+        key[r] = 0xFFFFFFFFu;
+        rb[r] = 0u;
+        cn[r] = 0u;
+        if (e < n) {
+            const unsigned long long x = src[e];
+            const uint32_t b = (uint32_t)(x >> 32);
+            key[r] = b;
+            cn[r] = (uint32_t)x;
+            const uint32_t bin = bin_mul ? __umulhi(b, bin_mul) : b;
+            rb[r] = (atomicAdd(&bins[bin], 1u) << 8) | bin;
+        }
+    }
+    __syncwarp();
+    {   // exclusive scan of the 256 bin sizes: 8 consecutive bins per lane
+        uint4 p = reinterpret_cast<uint4*>(bins)[2 * lane], q = reinterpret_cast<uint4*>(bins)[2 * lane + 1];
+        const uint32_t tot = p.x + p.y + p.z + p.w + q.x + q.y + q.z + q.w;
+        uint32_t inc = tot;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+            if (lane >= d) inc += v;
+        }
+        uint32_t run = inc - tot;
+        uint4 o0, o1;
+        o0.x = run; run += p.x;
+        o0.y = run; run += p.y;
+        o0.z = run; run += p.z;
+        o0.w = run; run += p.w;
+        o1.x = run; run += q.x;
+        o1.y = run; run += q.y;
+        o1.z = run; run += q.z;
+        o1.w = run;
+        __syncwarp();
+        reinterpret_cast<uint4*>(bins)[2 * lane] = o0;
+        reinterpret_cast<uint4*>(bins)[2 * lane + 1] = o1;
+    }
+    __syncwarp();
+    uint32_t start[K];
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        start[r] = bins[rb[r] & 255u];
+        if (r * 32 + lane < n) keys[start[r] + (rb[r] >> 8)] = key[r];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        if (r * 32 + lane < n) {
+            const uint32_t bin = rb[r] & 255u;
+            const uint32_t end = bin == 255u ? (uint32_t)n : bins[bin + 1u];
+            uint32_t pos = start[r];
+            for (uint32_t j = start[r]; j < end; ++j) pos += keys[j] < key[r] ? 1u : 0u;  // (keys of one dialogue are distinct)
+            fkeys[pos] = key[r];
+            cnts[pos] = cn[r];
+        }
+    }
+    __syncwarp();
+    // the ordered row leaves through shared memory so that the global stores are coalesced
+#pragma unroll
+    for (int r = 0; r < K; ++r) {
+        const int e = r * 32 + lane;
+        if (e < n) {
+            const uint32_t idx = fkeys[e];
+            const double c = (double)cnts[e];
+            oi[e] = (int32_t)idx;
+            ov[e] = idf ? __dmul_rn(c, __ldg(idf + idx)) : c;
+        }
+    }
+    __syncwarp();
+}
+
 __global__ void __launch_bounds__(32 * GATHER_WARPS, 4) k_gather_csr(unsigned long long* __restrict__ tmp, const long long* __restrict__ tmpoff,
                                                                      const long long* __restrict__ rowptr, long long n_rows,
-                                                                     const double* __restrict__ idf, int small_keys,
-                                                                     int32_t* __restrict__ out_idx, double* __restrict__ out_val) {
-    __shared__ uint32_t key_sh[GATHER_WARPS][512];
-    __shared__ uint32_t cnt_sh[GATHER_WARPS][512];
+                                                                     const double* __restrict__ idf, int small_keys, int even_keys,
+                                                                     uint32_t bin_mul, int rpw, int32_t* __restrict__ out_idx,
+                                                                     double* __restrict__ out_val) {
+    __shared__ __align__(16) uint32_t key_sh[GATHER_WARPS][512];
+    __shared__ __align__(16) uint32_t cnt_sh[GATHER_WARPS][512];
+    __shared__ __align__(16) uint32_t bin_sh[GATHER_WARPS][256];
+    __shared__ __align__(16) uint32_t fkey_sh[GATHER_WARPS][256];
     const int lane = threadIdx.x & 31;
     uint32_t* keys = key_sh[threadIdx.x >> 5];
     uint32_t* cnts = cnt_sh[threadIdx.x >> 5];
+    uint32_t* bins = bin_sh[threadIdx.x >> 5];
+    uint32_t* fkeys = fkey_sh[threadIdx.x >> 5];
+    // a warp takes rpw (<= 32) consecutive dialogues at a time: their row pointers and staging offsets are read by the 32 lanes at
+    // once (one coalesced round trip instead of three dependent ones per dialogue) and handed out by shuffles
     const long long nwarps = (long long)gridDim.x * GATHER_WARPS;
-    for (long long r = (long long)blockIdx.x * GATHER_WARPS + (threadIdx.x >> 5); r < n_rows; r += nwarps) {
-        const long long o = rowptr[r], nl = rowptr[r + 1] - o;
-        unsigned long long* src = tmp + tmpoff[r];
+    for (long long r0 = ((long long)blockIdx.x * GATHER_WARPS + (threadIdx.x >> 5)) * rpw; r0 < n_rows; r0 += nwarps * rpw) {
+      const long long mine = r0 + lane < n_rows ? r0 + lane : n_rows - 1;
+      const long long my_o = rowptr[mine], my_e = rowptr[mine + 1], my_t = tmpoff[mine];
+      const int nr = (int)(n_rows - r0 < rpw ? n_rows - r0 : rpw);
+      for (int k = 0; k < nr; ++k) {
+        const long long o = __shfl_sync(0xFFFFFFFFu, my_o, k), nl = __shfl_sync(0xFFFFFFFFu, my_e, k) - o;
+        unsigned long long* src = tmp + __shfl_sync(0xFFFFFFFFu, my_t, k);
         int32_t* oi = out_idx + o;
         double* ov = out_val + o;
+        if (even_keys && nl <= 256) {
+            const int n = (int)nl;
+            if (n <= 32) gather_counted_k<1>(src, n, keys, fkeys, cnts, bins, bin_mul, lane, idf, oi, ov);
+            else if (n <= 64) gather_counted_k<2>(src, n, keys, fkeys, cnts, bins, bin_mul, lane, idf, oi, ov);
+            else if (n <= 128) gather_counted_k<4>(src, n, keys, fkeys, cnts, bins, bin_mul, lane, idf, oi, ov);
+            else gather_counted_k<8>(src, n, keys, fkeys, cnts, bins, bin_mul, lane, idf, oi, ov);
+            continue;
+        }
         if (small_keys && nl <= 512) {
             const int n = (int)nl;
             if (n <= 32) gather_sorted_k<1>(src, n, keys, cnts, lane, idf, oi, ov);
@@ -736,6 +842,7 @@ __global__ void __launch_bounds__(32 * GATHER_WARPS, 4) k_gather_csr(unsigned lo
             oi[i] = (int32_t)idx;
             ov[i] = idf ? __dmul_rn(c, __ldg(idf + idx)) : c;
         }
+      }
     }
 }
 
@@ -845,10 +952,14 @@ cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long lon
         return cudaGetLastError();
     }
     k_scan_rowptr<<<nb, SCAN_BLOCK, 0, st>>>(nnz, n_rows, bsum, rowptr);
-    long long g = (n_rows + GATHER_WARPS - 1) / GATHER_WARPS;
+    const int rpw = (int)std::min<long long>(32, std::max<long long>(1, n_rows / 8192));  // dialogues per warp and round
+    long long g = (n_rows + rpw * GATHER_WARPS - 1) / (rpw * GATHER_WARPS);
     if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
-    k_gather_csr<<<(unsigned)g, 32 * GATHER_WARPS, 0, st>>>(tmp, tmpoff, rowptr, n_rows, h->m.idf, h->m.num_features <= (1 << 23) ? 1 : 0, out_idx,
-                                                       out_val);
+    // hashed buckets are evenly spread (counting sort); vocabulary indices are not (frequent terms have the low ones)
+    const int even_keys = h->m.vocab_cap ? 0 : 1;
+    const uint32_t bin_mul = h->m.num_features > 256 ? (uint32_t)((1ULL << 40) / (uint64_t)h->m.num_features) : 0u;
+    k_gather_csr<<<(unsigned)g, 32 * GATHER_WARPS, 0, st>>>(tmp, tmpoff, rowptr, n_rows, h->m.idf, h->m.num_features <= (1 << 23) ? 1 : 0, even_keys,
+                                                       bin_mul, rpw, out_idx, out_val);
     h->launches += 2;
     return cudaGetLastError();
 }
