@@ -36,8 +36,36 @@ def parse():
     ap.add_argument("--rows", type=int, default=1_000_000, help="dialogues per GPU")
     ap.add_argument("--tokens", type=int, default=200)
     ap.add_argument("--cpu-rows", type=int, default=1_000_000, help="bounded sample for the CPU baseline")
-    ap.add_argument("--stages", action="store_true", help="also time featurize->CSR and CSR scoring separately")
+    ap.add_argument("--stages", action="store_true", help="(kept for old command lines: the stage timings are always taken)")
+    ap.add_argument("--configs", default="c1,c3,c4,c5", help="other BASELINE.json configs measured after the headline one ('' = none)")
+    ap.add_argument("--config-rows", type=int, default=10_000_000, help="rows of C3 (total) and C5 (total / per GPU)")
     return ap.parse_args()
+
+
+def spark_probe():
+    """look for the reference's own runtime on this box instead of assuming it is absent."""
+    import shutil
+    out = {"java": shutil.which("java"), "spark_submit": shutil.which("spark-submit"), "pyspark": None}
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("pyspark")
+        out["pyspark"] = None if spec is None else (spec.origin or "found")
+    except Exception as e:  # a broken install counts as absent
+        out["pyspark"] = None
+        out["error"] = type(e).__name__
+    out["available"] = bool(out["java"] and out["pyspark"])
+    return out
+
+
+def kernel_source_hash():
+    """sha256 over the sources of the dialogue kernels: profiles/traffic.json is only quoted while it matches."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "fraud-detection-spark-kafka-llm_b200", "csrc")
+    for f in ("fd_main.cu", "fd_rows_dev.cuh", "fd_rows.cuh", "fd_common.cuh"):
+        with open(os.path.join(d, f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
 
 
 def peaks():
@@ -182,13 +210,15 @@ def main():
         ms = 1000.0 * float(np.mean(t))
         v = rows / (ms / 1000.0)
         cfg = workload_config(rows, a.tokens, stats, f"rows over {cores} host threads")
-        cfg["note"] = "Spark local[*] unavailable offline (no JVM/pyspark); CPU port of the oracle, oracle/oracle.c"
+        probe = spark_probe()
+        cfg["note"] = ("Spark local[*] " + ("found on this box but not wired in" if probe["available"] else "unavailable on this box (no JVM/pyspark)")
+                       + "; CPU port of the oracle, oracle/oracle.c")
         print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
                           "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                           "dtype": "u8/f64", "data": "synthetic", "config": cfg,
                           "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                            "sample": f"{rows} of the workload's dialogues per step"},
-                          "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+                          "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "spark_probe": probe}))
         return
 
     if not torch.cuda.is_available():
@@ -281,62 +311,106 @@ def main():
     clocks = sampler.stop()
     assert torch.equal(hp, pred.cpu()), "host-buffer path and device path disagree"
 
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+    # ---- what the host side of this box delivers at this N: the same bytes as bare pinned copies, all ranks at once
+    dst = torch.empty_like(pk.data)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        dst.copy_(hdata, non_blocking=True)
+    torch.cuda.synchronize(dev)
+    th = torch.tensor([(time.perf_counter() - t0) / 3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(th, op=dist.ReduceOp.MAX)
+    h2d_gbs = hdata.numel() / float(th.item()) / 1e9     # per rank, slowest rank
+    e2e_gbs = (stats["text_bytes"] + 8 * (n + 1)) / float(te.item()) / 1e9
+    del dst
 
-    peak, peak_src = peaks()
-    bytes_per_row = stats["L_bar"] + 8.0 + 40.0  # text + offset + three result columns (fused)
-    achieved = n * bytes_per_row / (ms_per_step / 1000.0) / 1e9
-    traffic = None
-    issue = None
-    tp = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tp):
-        with open(tp) as f:
-            cap = json.load(f)
-        per_dialogue = cap.get("k_rows_dt_clean_bytes_per_dialogue")
-        traffic = None if per_dialogue is None else per_dialogue * n  # DRAM bytes of one launch over this batch
-        ipd = cap.get("k_rows_dt_clean_warp_instructions_per_dialogue")
-        if ipd is not None and clocks.get("sm_mhz"):
-            # what actually bounds the kernel: warp-instruction issue (148 SMs x 4 schedulers x 1 instruction per clock);
-            # instructions per dialogue come from the committed ncu capture, the rate from this run
-            sms = torch.cuda.get_device_properties(dev).multi_processor_count
-            peak_issue = sms * 4 * clocks["sm_mhz"] * 1e6
-            ach_issue = ipd * n / (ms_per_step / 1000.0)
-            issue = {"bound": "warp-instruction issue", "warp_instructions_per_dialogue": ipd, "achieved": ach_issue / 1e9,
-                     "peak": peak_issue / 1e9, "unit": "G warp-instr/s", "frac": ach_issue / peak_issue,
-                     "source": "instructions per dialogue from the ncu capture in profiles/traffic.json"}
-    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
-           "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f64",
-           "data": "synthetic",
-           "config": workload_config(n, a.tokens, stats, f"rows sharded x{world}, no collective"),
-           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                        "kernel": "k_rows<DT,clean>", "bytes_per_dialogue": bytes_per_row, "peak_source": peak_src,
-                        "duration_ms": ms_per_step},
-           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(stats["text_bytes"] + 8 * (n + 1)),
-                   "d2h_bytes_per_step": int(40 * n), "ms_per_step": 1000.0 * float(te.item()), "pinned_numa": numa},
-           "gpu_launches": int(launches), "clocks": clocks, "issue_roofline": issue}
+    stages = stage_times(model, pk, dev, stats, peaks()[0])
+    del pred, prob, raw
+    torch.cuda.empty_cache()
 
-    # ---- CPU baseline on this box's host cores (bounded sample), rank 0 at N = 1 only
-    if world == 1:
-        rows_cpu = min(n, a.cpu_rows)
-        data_np, offs_np = hdata.numpy(), hoffs.numpy()[:rows_cpu + 1]
-        v, secs, cpu_out = cpu_port(model, data_np, offs_np, cores)
-        agree = bool(np.array_equal(cpu_out[0], hp.numpy()[:rows_cpu]) and np.array_equal(cpu_out[2], hr.numpy()[:rows_cpu]))
-        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                               "sample": f"first {rows_cpu} dialogues of the workload, {secs:.2f} s, oracle/oracle.c with {cores} threads; "
-                                         "Spark local[*]: unavailable on this box", "labels_and_raw_equal_gpu": agree}
-    if a.stages and world == 1:
-        out["stages"] = stage_times(model, pk, dev, stats)
-    print(json.dumps(out))
+    out = None
+    if rank == 0:
+        peak, peak_src = peaks()
+        bytes_per_row = stats["L_bar"] + 8.0 + 40.0  # text + offset + three result columns (fused)
+        achieved = n * bytes_per_row / (ms_per_step / 1000.0) / 1e9
+        traffic = None
+        issue = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            with open(tp) as f:
+                cap = json.load(f)
+            # the capture is only quoted while the kernel sources are the ones it was taken from
+            if cap.get("kernel_source_sha") == kernel_source_hash():
+                per_dialogue = cap.get("k_main_dt_clean_bytes_per_dialogue")
+                traffic = None if per_dialogue is None else per_dialogue * n  # DRAM bytes of one launch over this batch
+                ipd = cap.get("k_main_dt_clean_warp_instructions_per_dialogue")
+                if ipd is not None and clocks.get("sm_mhz"):
+                    # what actually bounds the kernel: warp-instruction issue (148 SMs x 4 schedulers x 1 instruction per
+                    # clock); instructions per dialogue come from the committed ncu capture, the rate from this run
+                    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+                    peak_issue = sms * 4 * clocks["sm_mhz"] * 1e6
+                    ach_issue = ipd * n / (ms_per_step / 1000.0)
+                    issue = {"bound": "warp-instruction issue", "warp_instructions_per_dialogue": ipd, "achieved": ach_issue / 1e9,
+                             "peak": peak_issue / 1e9, "unit": "G warp-instr/s", "frac": ach_issue / peak_issue,
+                             "source": "instructions per dialogue from the ncu capture in profiles/traffic.json (" + str(cap.get("capture")) + ")"}
+        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+               "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f64",
+               "data": "synthetic",
+               "config": workload_config(n, a.tokens, stats, f"rows sharded x{world}, no collective"),
+               "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                            "kernel": "k_main<DT,clean>", "bytes_per_dialogue": bytes_per_row, "peak_source": peak_src,
+                            "duration_ms": ms_per_step},
+               "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(stats["text_bytes"] + 8 * (n + 1)),
+                       "d2h_bytes_per_step": int(40 * n), "ms_per_step": 1000.0 * float(te.item()), "pinned_numa": numa,
+                       "h2d_gbs_per_gpu": e2e_gbs, "h2d_ceiling_gbs": h2d_gbs, "frac_of_ceiling": e2e_gbs / h2d_gbs,
+                       "ceiling": "bare pinned cudaMemcpyAsync of the same text bytes, all ranks at once, slowest rank"},
+               "gpu_launches": int(launches), "clocks": clocks, "issue_roofline": issue, "stages": stages,
+               "spark_probe": spark_probe()}
+        # ---- CPU baseline on this box's host cores (bounded sample), rank 0 at N = 1 only
+        if world == 1:
+            rows_cpu = min(n, a.cpu_rows)
+            data_np, offs_np = hdata.numpy(), hoffs.numpy()[:rows_cpu + 1]
+            v, secs, cpu_out = cpu_port(model, data_np, offs_np, cores)
+            agree = bool(np.array_equal(cpu_out[0], hp.numpy()[:rows_cpu]) and np.array_equal(cpu_out[2], hr.numpy()[:rows_cpu]))
+            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": f"first {rows_cpu} dialogues of the workload, {secs:.2f} s, oracle/oracle.c with {cores} threads; "
+                                             "Spark local[*]: " + ("found on this box but not wired in" if out["spark_probe"]["available"] else "unavailable on this box"),
+                                   "labels_and_raw_equal_gpu": agree}
+    # ---- the other BASELINE.json configs, same process, same N (C3 and C5 run on every rank)
+    del hdata, hoffs, hp, hq, hr, pk, model
+    torch.cuda.empty_cache()
+    want = [c for c in a.configs.split(",") if c]
+    if want:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import bench_configs as bc
+        ctx = bc.Ctx()
+        cfgs = {}
+        for name in want:
+            t0 = time.perf_counter()
+            try:
+                if name == "c3":
+                    res = bc.run_c3(ctx, a.config_rows)
+                elif name == "c5":
+                    res = bc.run_c5(ctx, a.config_rows)
+                else:
+                    res = bc.RUNNERS[name](ctx)
+            except Exception as e:  # a failed side measurement must not take the headline line with it
+                res = {"error": f"{type(e).__name__}: {e}"[:300]} if rank == 0 else None
+            if res is not None:
+                res["wall_s"] = round(time.perf_counter() - t0, 1)
+                cfgs[name] = res
+        if out is not None:
+            out["configs"] = cfgs
+    if out is not None:
+        print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
 
-def stage_times(model, pk, dev, stats):
+def stage_times(model, pk, dev, stats, peak):
     """featurize -> CSR and CSR -> score timed separately through the C-ABI with preallocated outputs
-    (3 repetitions each after one warm-up)."""
+    (3 repetitions each after one warm-up), each with its own roofline object (SURVEY.md 8d algorithmic bytes)."""
     import torch
     res = {}
     n = pk.n_rows
@@ -360,7 +434,10 @@ def stage_times(model, pk, dev, stats):
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1) / 3
     b = stats["text_bytes"] + 8 * n + 12 * nnz + 8 * n
-    res["featurize_csr"] = {"ms": ms, "dialogues_per_s": n / ms * 1e3, "algorithmic_GBps": b / ms / 1e6, "nnz": nnz}
+    res["featurize_csr"] = {"ms": ms, "dialogues_per_s": n / ms * 1e3, "nnz": nnz,
+                            "roofline": {"bound": "hbm", "achieved": b / ms / 1e6, "peak": peak, "unit": "GB/s", "frac": b / ms / 1e6 / peak,
+                                         "bytes_per_dialogue": b / n, "traffic": None,
+                                         "kernels": "k_main<CSR,clean> + k_scan_* + k_gather_csr (whole fd_featurize call, incl. its host read-back of nnz)"}}
     pred = torch.empty(n, dtype=torch.float64, device=dev)
     prob = torch.empty((n, 2), dtype=torch.float64, device=dev)
     raw = torch.empty((n, 2), dtype=torch.float64, device=dev)
@@ -376,7 +453,10 @@ def stage_times(model, pk, dev, stats):
     e1.record()
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1) / 3
-    res["score_csr"] = {"ms": ms, "dialogues_per_s": n / ms * 1e3, "algorithmic_GBps": (12 * nnz + 48 * n) / ms / 1e6}
+    b = 12 * nnz + 48 * n
+    res["score_csr"] = {"ms": ms, "dialogues_per_s": n / ms * 1e3,
+                        "roofline": {"bound": "hbm", "achieved": b / ms / 1e6, "peak": peak, "unit": "GB/s", "frac": b / ms / 1e6 / peak,
+                                     "bytes_per_dialogue": b / n, "traffic": None, "kernels": "k_score_csr"}}
     return res
 
 

@@ -25,6 +25,7 @@ EPSILON = 2.220446049250313e-16  # ml.impl.Utils.EPSILON
 MAX_BINS_SUPPORTED = 32
 SEG_LEN = 8192                   # column entries per histogram work unit
 MAX_ITEMS_PER_GROUP = 1 << 21    # (node, feature) items per histogram pass: 2M x 256 B = 512 MiB
+PROFILE_DEFAULT = False          # new trainers time their phases (with device synchronisation) when set
 
 
 # ------------------------------------------------------------------------------------------ findSplits
@@ -450,7 +451,7 @@ class ForestTrainer:
         self.min_instances, self.min_info_gain = int(min_instances_per_node), float(min_info_gain)
         self.strategy, self.rate, self.seed, self.prune = feature_subset_strategy, float(subsampling_rate), int(seed), bool(prune)
         self.stats: Dict[str, float] = {}
-        self.profile = False  # when set, phases are timed with a device synchronise on both sides (slower)
+        self.profile = PROFILE_DEFAULT  # when set, phases are timed with a device synchronise on both sides (slower)
         self._t: Dict[str, float] = {}
 
     def _tick(self, name: str, t0: float) -> float:
