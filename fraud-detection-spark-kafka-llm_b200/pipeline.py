@@ -388,22 +388,37 @@ class Pipeline:
                 pk = pk.to_device(torch.device("cuda", hnd.device))
                 feats[i] = st.fit_packed(hnd, pk, flags)
                 batch, cleaned = pk, not bool(flags & _lib.FD_FLAG_CLEAN)
+        import time
+        from . import training as _training
+        prof = _training.PROFILE_DEFAULT  # phase timers (they synchronise the device)
+        ph: Dict[str, float] = {}
+
+        def tick(name, t0):
+            if prof:
+                torch.cuda.synchronize()
+                ph[name] = ph.get(name, 0.0) + time.perf_counter() - t0
+            return time.perf_counter()
+
+        tt = time.perf_counter()
         tf_model = PipelineModel(feats)
         rowptr, idx, val = tf_model.featurize(batch, cleaned=cleaned, device=device)
+        tt = tick("featurize", tt)
         dev = rowptr.device
         nf = tf_model._plan.num_features
         fitted: List[S.Stage] = list(feats)
         if idf:
             st = idf[0]
             if isinstance(st, S.IDF):
-                df = torch.bincount(idx[val > 0].long(), minlength=nf)
+                # docFreq[j] = documents with value > 0 at j (term counts are >= 1, so normally every stored entry counts)
+                df = torch.bincount(idx if bool((val > 0).all()) else idx[val > 0], minlength=nf)
                 nd = torch.tensor([rowptr.numel() - 1], dtype=torch.int64, device=dev)
                 if dist.is_available() and dist.is_initialized():
                     dist.all_reduce(df)
                     dist.all_reduce(nd)
                 st = st.fit_from_doc_freq(df.cpu().numpy(), int(nd.item()))
             fitted.append(st)
-            val = val * torch.from_numpy(st.idf).to(dev)[idx.long()]  # IDFModel.transform: one exact fp64 multiply
+            val.mul_(torch.from_numpy(st.idf).to(dev)[idx])  # IDFModel.transform: one exact fp64 multiply
+            tt = tick("idf fit+transform", tt)
         if est:
             c = est[0]
             if isinstance(c, S._TreeEstimator):
@@ -411,6 +426,9 @@ class Pipeline:
                 lab = lab.to(dev).to(torch.uint8)
                 c = c.fit_csr(tf_model.handle(device), rowptr, idx, val, lab, nf, **explicit)
                 c.paramMap.setdefault("featuresCol", fitted[-1].getOrDefault("outputCol"))
+                tt = tick("tree estimator", tt)
+                if prof and hasattr(c, "trainer_stats"):
+                    c.trainer_stats["pipeline_phases_s"] = dict(ph)
             fitted.append(c)
         return PipelineModel(fitted)
 

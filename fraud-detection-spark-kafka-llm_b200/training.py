@@ -483,22 +483,20 @@ class ForestTrainer:
             pos = start + (torch.arange(int(cnt.sum()), device=rowptr.device) - first)
             sel_f, sel_v = idx[pos], val[pos]
         if dist is not None and dist.get_world_size() > 1:
-            # every rank needs the SAME sample: all-gather the sampled entries (padded to the longest shard)
+            # every rank needs the SAME sample.  The exchange uses all-reduce only (the collective the histograms use, so
+            # no second set of channels has to be set up): sizes first, then every rank adds its entries into its own slice
+            # of a zero buffer -- sums with zeros are exact, feature ids are exact in fp64
             ws = dist.get_world_size()
-            n_loc = torch.tensor([sel_f.numel()], dtype=torch.int64, device=sel_f.device)
-            sizes = [torch.zeros_like(n_loc) for _ in range(ws)]
-            dist.all_gather(sizes, n_loc)
-            mx = int(max(int(x.item()) for x in sizes))
-            pf = torch.zeros(mx, dtype=torch.int32, device=sel_f.device)
-            pv = torch.zeros(mx, dtype=torch.float64, device=sel_f.device)
-            pf[:sel_f.numel()] = sel_f
-            pv[:sel_v.numel()] = sel_v
-            gf = [torch.empty_like(pf) for _ in range(ws)]
-            gv = [torch.empty_like(pv) for _ in range(ws)]
-            dist.all_gather(gf, pf)
-            dist.all_gather(gv, pv)
-            sel_f = torch.cat([g[:int(n.item())] for g, n in zip(gf, sizes)])
-            sel_v = torch.cat([g[:int(n.item())] for g, n in zip(gv, sizes)])
+            sizes = torch.zeros(ws, dtype=torch.int64, device=sel_f.device)
+            sizes[rank] = sel_f.numel()
+            dist.all_reduce(sizes)
+            sz = sizes.cpu().tolist()
+            off = int(sum(sz[:rank]))
+            buf = torch.zeros((int(sum(sz)), 2), dtype=torch.float64, device=sel_f.device)
+            buf[off:off + sel_f.numel(), 0] = sel_f.to(torch.float64)
+            buf[off:off + sel_f.numel(), 1] = sel_v
+            dist.all_reduce(buf)
+            sel_f, sel_v = buf[:, 0].to(torch.int32), buf[:, 1].contiguous()
         num_splits = min(self.max_bins, n_total) - 1
         return find_splits_torch(sel_f, sel_v, self.F, fraction * n_total, num_splits)
 
@@ -665,6 +663,8 @@ class ForestTrainer:
             ln = np.stack([2 * cn, 2 * cn + 1], 1).reshape(-1).astype(np.int32)
             ls = np.stack([cl, cr], 1).reshape(-1, 2).astype(np.float64)
             tt = self._tick("kernel:advance", tt)
-        self.stats = {"phases_s": dict(self._t), "hist_bytes": float(hist_bytes), "allreduce_calls": float(allreduce_calls), "n_total": float(n_total)}
         cat = [np.concatenate([lv[c] for lv in levels]) for c in range(7)]
-        return trees_from_levels(self.T, cat[0], cat[1], cat[2], cat[3], cat[4], cat[5], cat[6], self.prune)
+        trees = trees_from_levels(self.T, cat[0], cat[1], cat[2], cat[3], cat[4], cat[5], cat[6], self.prune)
+        tt = self._tick("host:assemble trees", tt)
+        self.stats = {"phases_s": dict(self._t), "hist_bytes": float(hist_bytes), "allreduce_calls": float(allreduce_calls), "n_total": float(n_total)}
+        return trees

@@ -248,7 +248,9 @@ def run_c5(ctx, rows=10_000_000, trees=100, depth=10, weak=True):
         stats = dict(getattr(rf, "trainer_stats", {}))
         stats.pop("phases_s", None)
         psecs, pmodel, _ = _c5_fit(ctx, n_local, trees, depth, profile=True)
-        phases = dict(getattr(pmodel.stages[-1], "trainer_stats", {}).get("phases_s", {}))
+        pstats = getattr(pmodel.stages[-1], "trainer_stats", {})
+        phases = dict(pstats.get("phases_s", {}))
+        phases.update({"pipeline:" + k: v for k, v in pstats.get("pipeline_phases_s", {}).items()})
         out[name] = {"rows_total": n_local * ctx.world, "rows_per_gpu": n_local, "fit_seconds": secs, "rows_per_s": n_local * ctx.world / secs,
                      "trees_per_s": trees / secs, "nodes": sum(t.n_nodes for t in rf.trees), "test_auc": float(auc),
                      "allreduce_calls": stats.get("allreduce_calls"), "hist_bytes": stats.get("hist_bytes"),
