@@ -561,6 +561,10 @@ class ForestTrainer:
         if dist is not None:
             dist.all_reduce(root)
         root = root.cpu().numpy()
+        # histogram cells are 32-bit and summed over ranks as int32: no cell can exceed a tree's total bag weight
+        if root.size and float(root.sum(axis=1).max()) >= 2.0 ** 31:
+            raise ValueError("the total bag weight of a tree reaches 2^31: histogram cells (int32, all-reduced) could overflow; "
+                             "train on fewer rows per forest or lower subsamplingRate")
         k = features_per_node(self.strategy, self.T, self.F)
         batch_fn = default_subset_batch(self.seed, self.F, k, dev) if subset_fn is None else None
         d_col_len = csc[0][1:] - csc[0][:-1]

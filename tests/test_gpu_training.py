@@ -249,3 +249,58 @@ def test_bag_poisson_kernel(fd):
         assert torch.equal(root, exp_root)
         short, _ = b.bag_poisson(1234, rate, T, lab[:1001])
         assert torch.equal(short, bagw[:, :1001])
+
+
+def test_root_histogram_at_scale_equals_bincount(fd):
+    """A C5-sized self-check that needs no oracle: the root-level histogram of fd_rf_histogram over 6M rows / 120M entries
+    (columns of up to several hundred segments, u32 cells in the tens of millions) equals torch.bincount over the same
+    (item, bin, label) triples weighted by the bag weights."""
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev)
+    g.manual_seed(12)
+    n, per_row, F = 6_000_000, 20, 4096
+    # feature ids skewed towards the low ones (long columns), distinct inside a row by construction: base + stride * j
+    base = (torch.rand(n, generator=g, device=dev) ** 3 * 64).long()
+    stride = torch.randint(1, F // per_row, (n,), generator=g, device=dev)
+    idx = (base[:, None] + stride[:, None] * torch.arange(per_row, device=dev)[None, :]).to(torch.int32).reshape(-1)
+    assert int(idx.max()) < F
+    nnz = idx.numel()
+    bins = torch.randint(0, 32, (nnz,), generator=g, device=dev, dtype=torch.uint8)
+    bins[torch.rand(nnz, generator=g, device=dev) < 0.9] = 3  # most of a column in one bin: cells in the millions
+    labels = (torch.rand(n, generator=g, device=dev) < 0.4).to(torch.uint8)
+    bagw = torch.randint(0, 6, (2, n), generator=g, device=dev, dtype=torch.uint8)
+    # CSC exactly as ForestTrainer.fit lays it out
+    row_of = torch.arange(n, dtype=torch.int32, device=dev).repeat_interleave(per_row)
+    order = torch.argsort(idx, stable=True)
+    row_lab = row_of | (labels.to(torch.int32) << 31).repeat_interleave(per_row)
+    colptr = torch.zeros(F + 1, dtype=torch.int64, device=dev)
+    torch.cumsum(torch.bincount(idx, minlength=F), 0, out=colptr[1:])
+    csc = (colptr, row_lab[order].contiguous(), bins[order].contiguous())
+    state = bagw.to(torch.int32) | (1 << 8)
+    feats = torch.cat([torch.arange(0, 40, device=dev), torch.randint(40, F, (260,), generator=g, device=dev)]).to(torch.int32)
+    tree = 1
+    items = (torch.full_like(feats, tree), torch.ones_like(feats), feats)
+    backend = training.CudaTreeBackend(fd.Handle(0))
+    units = training._units_device(colptr[1:] - colptr[:-1], feats.long())
+    assert int(units[0].numel()) > feats.numel() + 500, "the test is meant to cover segmented columns"
+    hist = backend.histogram(csc, state, items, units).to(torch.int64)
+    # reference: every entry whose feature is in the item list (duplicates in the list each get the full count)
+    w = bagw[tree].to(torch.int64)[row_of.long()]
+    key = idx.long() * 64 + bins.long() * 2 + labels.long().repeat_interleave(per_row)
+    per_feature = torch.bincount(key, weights=w.double(), minlength=F * 64).view(F, 32, 2).round().to(torch.int64)
+    assert torch.equal(hist, per_feature[feats.long()])
+    assert int(hist.max()) > 1_000_000 and int(hist.sum()) > 0
+
+
+def test_bag_weight_overflow_guard(fd):
+    """Histogram cells are int32 after the all-reduce: a forest whose total bag weight per tree reaches 2^31 is refused."""
+    h = fd.Handle(0)
+    tr = training.ForestTrainer(training.CudaTreeBackend(h), 4, n_trees=2, max_depth=2, feature_subset_strategy="all", seed=1)
+    n = 9_000_000
+    rowptr = torch.arange(n + 1, dtype=torch.int64, device="cuda")
+    idx = torch.zeros(n, dtype=torch.int32, device="cuda")
+    val = torch.ones(n, dtype=torch.float64, device="cuda")
+    labels = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    bag = torch.full((2, n), 255, dtype=torch.uint8, device="cuda")
+    with pytest.raises(ValueError, match="2\\^31"):
+        tr.fit(rowptr, idx, val, labels, bag_weights=bag, subset_fn=lambda t, node: np.arange(4, dtype=np.int32))
