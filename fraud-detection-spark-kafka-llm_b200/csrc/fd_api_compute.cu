@@ -10,7 +10,8 @@ namespace fd {
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 constexpr size_t SLOT_CTRL = 256;
-constexpr size_t SLOT_BIGTABS = wide_pool_slots(MED_CTAS, BIG_WORKERS) * 8;
+constexpr size_t SLOT_MEDTABS = med_pool_slots(MED_CTAS) * 8;
+constexpr size_t SLOT_BIGTABS = SLOT_MEDTABS + big_pool_slots(BIG_WORKERS) * 8;  // two disjoint pools (the variants run side by side)
 // scratch slot = control block, wide tables, per-warp spill tables, then the deferred-dialogue list with ONE ENTRY PER DIALOGUE of the
 // call (every dialogue may be deferred, so the list can never overflow)
 constexpr size_t SLOT_SPILL = SPILL_SLOTS * 8;
@@ -19,6 +20,7 @@ static size_t slot_bytes(long long n_rows) { return align_up(SLOT_CTRL + SLOT_BI
 static void fill_slot(RowArgs& a, char* base, long long n_rows) {
     a.ctrl = reinterpret_cast<Ctrl*>(base);
     a.big_tabs = reinterpret_cast<unsigned long long*>(base + SLOT_CTRL);
+    a.big2_tabs = reinterpret_cast<unsigned long long*>(base + SLOT_CTRL + SLOT_MEDTABS);
     a.spill_tabs = reinterpret_cast<unsigned long long*>(base + SLOT_CTRL + SLOT_BIGTABS);
     a.big_rows = reinterpret_cast<long long*>(base + SLOT_CTRL + SLOT_BIGTABS + SLOT_SPILL);
     a.big_cap = n_rows;
@@ -80,6 +82,7 @@ static int run_featurize_pass(fd_handle* h, const uint8_t* text, const int64_t* 
     h->tmp_cap = tmp_cap;
     RowArgs a;
     memset(&a, 0, sizeof(a));
+    a.host_bytes = -1;
     a.text = text;
     a.offs = offs;
     a.n_rows = n_rows;
@@ -205,6 +208,7 @@ int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev,
     h->feat_rows = -1;  // (the scratch slot overlaps the staging arrays of an unfinished fd_featurize_begin)
     RowArgs a;
     memset(&a, 0, sizeof(a));
+    a.host_bytes = -1;
     a.text = text_dev;
     a.offs = offs_dev;
     a.n_rows = n_rows;
@@ -235,6 +239,7 @@ int fd_vocab_count(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_de
     h->feat_rows = -1;  // (as in fd_transform)
     RowArgs a;
     memset(&a, 0, sizeof(a));
+    a.host_bytes = -1;
     a.text = text_dev;
     a.offs = offs_dev;
     a.n_rows = n_rows;
@@ -335,6 +340,7 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
         cudaStream_t st = h->hs[s];
         RowArgs a;
         memset(&a, 0, sizeof(a));
+    a.host_bytes = -1;
         fill_slot(a, base, nr);
         if (nbytes > 0)
             FD_CUDA(h, cudaMemcpyAsync(base + off_text + d, text_host + b0, (size_t)nbytes, cudaMemcpyHostToDevice, st));
@@ -343,6 +349,7 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
         a.offs = reinterpret_cast<const int64_t*>(base + off_offs);
         a.n_rows = nr;
         a.flags = flags;
+        a.host_bytes = nbytes;  // (the offsets are host memory here: the kernel shape is picked without a device round trip)
         a.m = h->m;  // (after prepare_fused)
         a.pred = reinterpret_cast<double*>(base + off_pred);
         a.prob = reinterpret_cast<double*>(base + off_prob);

@@ -32,7 +32,7 @@ struct Ctrl {
     unsigned int big2_count;        // dialogues deferred to the large wide-table kernel (list grows from the back)
     unsigned int tmp_overflow;      // staging buffer was too small
     int status;                     // sticky device-side status (FD_OK / FD_ERR_LIMIT); NOT cleared per call
-    int shape;                      // kernel shape picked on the device for this call (8 or 9, see fd_rows.cuh)
+    int shape;                      // (unused: the kernel shape is derived from the offsets by the kernels themselves)
     unsigned int pad[1];
 };
 

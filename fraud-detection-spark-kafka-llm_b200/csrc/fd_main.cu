@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const Model& m = a.m;
-    if (a.pick_shape && a.ctrl->shape != TL) return;  // the other shape was picked for this call
+    if (a.pick_shape && shape_for(a.offs[a.n_rows] - a.offs[0], a.n_rows, a.pick_keep) != TL) return;  // the other shape runs this call
 
     // ---- CTA-shared tables
     uint4* lut = reinterpret_cast<uint4*>(smem_raw);
@@ -692,14 +692,20 @@ static cudaError_t launch_shapes(fd_handle* h, const RowArgs& a0, cudaStream_t s
         return a.m.dt_stop ? launch_k<MODE_DT, CLEAN, 8, 2, POW2>(h, a, st) : launch_k<MODE_DT, CLEAN, 8, 1, POW2>(h, a, st);
     }
     a.m.dt_small = 0;  // (the generic path below keeps a full count table; the wide-table kernels see the caller's model)
-    cudaError_t e;
+    a.pick_shape = 0;
     if (a.n_rows >= ROWS_FOR_SMALL_TABLES) {
-        // large batches let the device choose the shape from the mean dialogue length: both are launched and the one
-        // that was not picked exits at once
-        a.pick_shape = 1;
-        launch_pick_shape(h, a, (MODE == MODE_LINEAR && a.m.filt_on) ? a.m.lr_keep : 1.0f, st);
-        e = launch_k<MODE, CLEAN, 8, 0, POW2>(h, a, st);
-        if (e != cudaSuccess) return e;
+        // large batches take the 256-slot shape when their dialogues are short.  A caller that holds the offsets on the host
+        // says how many bytes the batch has and the shape is picked here; otherwise both shapes are launched and each CTA
+        // finds out from the offsets whether its shape is the one that runs (the other exits at once)
+        const float keep = (MODE == MODE_LINEAR && a.m.filt_on) ? a.m.lr_keep : 1.0f;
+        if (a.host_bytes >= 0) {
+            if (shape_for(a.host_bytes, a.n_rows, keep) == 8) return launch_k<MODE, CLEAN, 8, 0, POW2>(h, a, st);
+        } else {
+            a.pick_shape = 1;
+            a.pick_keep = keep;
+            const cudaError_t e = launch_k<MODE, CLEAN, 8, 0, POW2>(h, a, st);
+            if (e != cudaSuccess) return e;
+        }
     }
     return launch_k<MODE, CLEAN, 9, 0, POW2>(h, a, st);
 }

@@ -84,6 +84,7 @@ extern "C" int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const
     cudaStream_t st = (cudaStream_t)stream;
     RowArgs a;
     memset(&a, 0, sizeof(a));
+    a.host_bytes = -1;
     a.text = text_dev;
     a.offs = offs_dev;
     a.n_rows = n_rows;
@@ -91,6 +92,7 @@ extern "C" int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const
     a.m = h->m;  // (after prepare_fused)
     a.ctrl = reinterpret_cast<Ctrl*>(base);
     a.big_tabs = reinterpret_cast<unsigned long long*>(base + NA_CTRL);
+    a.big2_tabs = a.big_tabs;  // one pool: the two wide-table kernels run one after the other here
     a.spill_tabs = nullptr;  // (a fixed scratch array cannot hold a table per warp: overflowing dialogues are deferred)
     a.big_rows = reinterpret_cast<long long*>(base + NA_CTRL + NA_TABS);
     a.big_cap = NOALLOC_MAX_ROWS;
@@ -99,7 +101,7 @@ extern "C" int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const
     a.raw = out_raw_dev;
     // the array still holds the previous call's counters and status: they must start at zero
     FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, sizeof(Ctrl), st));
-    if (n_rows > 0) FD_CUDA(h, launch_rows_workers(h, mode, a, NOALLOC_MED_CTAS, NOALLOC_WORKERS, st));
+    if (n_rows > 0) FD_CUDA(h, launch_rows_workers(h, mode, a, NOALLOC_MED_CTAS, NOALLOC_WORKERS, false, st));
     if (out_status_dev)
         FD_CUDA(h, cudaMemcpyAsync(out_status_dev, &a.ctrl->status, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
     return FD_OK;

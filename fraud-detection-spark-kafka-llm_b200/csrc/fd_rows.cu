@@ -28,9 +28,10 @@ namespace fd {
 // the kernel
 // ------------------------------------------------------------------------------------------------
 // BIG = 0: main kernel (count table in shared memory); 1: medium wide tables (8 warps per CTA); 2: large wide tables
+// (the body is a device function: k_rows runs one variant per launch, k_wide runs the two wide-table variants side by side;
+//  bid / nblocks = this CTA's index and the CTA count WITHIN its variant)
 template <int MODE, bool CLEAN, int BIG, int TL>
-__global__ void __launch_bounds__(BIG == 2 ? 32 : (BIG == 1 ? 32 * MED_WARPS : 32 * row_warps(TL)), BIG ? 1 : (TL == 8 ? 2 : 3))
-k_rows(const RowArgs a) {
+__device__ __forceinline__ void rows_body(const RowArgs& a, const int bid, const int nblocks) {
     constexpr int ROW_WARPS = BIG == 2 ? 1 : (BIG == 1 ? MED_WARPS : row_warps(TL));
     constexpr int TAB_LOG2 = TL;
     using WarpSmemT = WarpSmem<TL>;
@@ -42,11 +43,11 @@ k_rows(const RowArgs a) {
     uint4* sww = reinterpret_cast<uint4*>(smem_raw + m.sw_tab_bytes());
     WarpSmemT& S = *reinterpret_cast<WarpSmemT*>(smem_raw + m.sw_smem_bytes() + (size_t)warp * sizeof(WarpSmemT));
 
-    if (BIG && (long long)blockIdx.x * ROW_WARPS >= (long long)(BIG == 1 ? a.ctrl->big_count : a.ctrl->big2_count))
+    if (BIG && (long long)bid * ROW_WARPS >= (long long)(BIG == 1 ? a.ctrl->big_count : a.ctrl->big2_count))
         return;  // nothing deferred to this CTA
-    if (!BIG && a.pick_shape && a.ctrl->shape != TL) return;  // the other shape was picked for this call
-    for (int i = threadIdx.x; i < (int)(m.sw_tab_bytes() / 4); i += blockDim.x) swt[i] = m.sw_tab[i];
-    for (int i = threadIdx.x; i < m.n_sw; i += blockDim.x) sww[i] = m.sw_words[i];
+    if (!BIG && a.pick_shape && shape_for(a.offs[a.n_rows] - a.offs[0], a.n_rows, a.pick_keep) != TL) return;  // the other shape runs this call
+    for (int i = threadIdx.x; i < (int)(m.sw_tab_bytes() / 4); i += 32 * ROW_WARPS) swt[i] = m.sw_tab[i];
+    for (int i = threadIdx.x; i < m.n_sw; i += 32 * ROW_WARPS) sww[i] = m.sw_words[i];
     if (lane == 0) {
         mbar_init(&S.mbar[0], 1);
         mbar_init(&S.mbar[1], 1);
@@ -54,14 +55,14 @@ k_rows(const RowArgs a) {
     }
     if (lane < 4) S.lmask[32 + lane] = 0u;
 
-    unsigned long long* tab = BIG == 1 ? a.big_tabs + ((size_t)(blockIdx.x * MED_WARPS + warp) << MED_LOG2)
-                            : (BIG == 2 ? a.big_tabs + ((size_t)blockIdx.x << BIG_LOG2) : S.tab);
+    unsigned long long* tab = BIG == 1 ? a.big_tabs + ((size_t)(bid * MED_WARPS + warp) << MED_LOG2)
+                            : (BIG == 2 ? a.big2_tabs + ((size_t)bid << BIG_LOG2) : S.tab);
     // table size: fixed in shared memory; in the wide-table kernel it follows the dialogue (a dialogue of b bytes
     // has at most b/2 + 1 tokens), so clearing it costs in proportion to the dialogue, not to the 2^16 maximum
     int TLOG2 = TAB_LOG2;
     const long long n_items = BIG == 1 ? (long long)a.ctrl->big_count : (BIG == 2 ? (long long)a.ctrl->big2_count : a.n_rows);
-    const long long stride = (long long)gridDim.x * ROW_WARPS;
-    long long item = (long long)blockIdx.x * ROW_WARPS + warp;
+    const long long stride = (long long)nblocks * ROW_WARPS;
+    long long item = (long long)bid * ROW_WARPS + warp;
     // deferred lists: medium dialogues from the front of big_rows, large ones from its back
     auto deferred_row = [&](long long i) { return BIG == 1 ? a.big_rows[i] : a.big_rows[a.big_cap - 1 - i]; };
     if (BIG && item < n_items) {
@@ -77,7 +78,8 @@ k_rows(const RowArgs a) {
         uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);  // count = 0, key = EMPTY
         for (int i = lane; i < (1 << TLOG2) / 2; i += 32) reinterpret_cast<uint4*>(tab)[i] = ff;
     }
-    __syncthreads();
+    if (BIG == 2) __syncwarp();  // (one warp per CTA of this variant; inside k_wide the CTA's other warps have left)
+    else __syncthreads();
     if (item >= n_items) return;
 
     const uint8_t* text = a.text;
@@ -334,7 +336,7 @@ k_rows(const RowArgs a) {
             constexpr int TPL = 1;  // tokens per lane per iteration (2 was measured slower: more idle lanes in the last iteration, 79 registers)
             for (int t0 = t_first; t0 < Tc; t0 += 32 * TPL) {
                 if (D + 32u * TPL > (3u << TLOG2) / 4u) {  // keep the table at most 3/4 full
-                    const long long gw = (long long)blockIdx.x * ROW_WARPS + warp;
+                    const long long gw = (long long)bid * ROW_WARPS + warp;
                     if (TL == 9 && BIG == 0 && tab == S.tab && a.spill_tabs != nullptr && gw < SPILL_WARPS) {
                         // carry on in this warp's own wide table: clear it, move the entries over, switch
                         unsigned long long* wt = a.spill_tabs + ((size_t)gw << MED_LOG2);
@@ -579,6 +581,24 @@ k_rows(const RowArgs a) {
     }
 }
 
+
+template <int MODE, bool CLEAN, int BIG, int TL>
+__global__ void __launch_bounds__(BIG == 2 ? 32 : (BIG == 1 ? 32 * MED_WARPS : 32 * row_warps(TL)), BIG ? 1 : (TL == 8 ? 2 : 3))
+k_rows(const RowArgs a) {
+    rows_body<MODE, CLEAN, BIG, TL>(a, (int)blockIdx.x, (int)gridDim.x);
+}
+
+// Both wide-table variants in ONE launch: CTAs [0, med_ctas) take the medium dialogues (8 warps each), the following
+// big_workers CTAs the large ones (their first warp only).  With nothing deferred every CTA leaves after one load.
+template <int MODE, bool CLEAN>
+__global__ void __launch_bounds__(32 * MED_WARPS, 1) k_wide(const RowArgs a, const int med_ctas, const int big_workers) {
+    if ((int)blockIdx.x < med_ctas) {
+        rows_body<MODE, CLEAN, 1, 9>(a, (int)blockIdx.x, med_ctas);
+    } else {
+        if (threadIdx.x >= 32) return;
+        rows_body<MODE, CLEAN, 2, 9>(a, (int)blockIdx.x - med_ctas, big_workers);
+    }
+}
 
 // ------------------------------------------------------------------------------------------------
 // CSR assembly: exclusive scan of per-dialogue nnz, then gather staging -> (idx, tf * idf)
@@ -849,13 +869,6 @@ __global__ void __launch_bounds__(32 * GATHER_WARPS, 4) k_gather_csr(unsigned lo
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
-// large batches: pick the kernel shape from the mean dialogue length, on the device (no host synchronisation)
-// (keep: the fraction of a dialogue's terms that reach the count table -- below 1 for a sparse LogisticRegression)
-__global__ void k_pick_shape(const int64_t* __restrict__ offs, long long n_rows, float keep, Ctrl* ctrl) {
-    const long long mean = (offs[n_rows] - offs[0]) / (n_rows > 0 ? n_rows : 1);
-    ctrl->shape = (float)mean * keep <= (float)MEAN_BYTES_FOR_SMALL_TABLES ? 8 : 9;
-}
-
 template <int MODE, bool CLEAN, int TL>
 static cudaError_t launch_main(fd_handle* h, const RowArgs& a, cudaStream_t st) {
     constexpr int NW = row_warps(TL);
@@ -874,33 +887,51 @@ static cudaError_t launch_main(fd_handle* h, const RowArgs& a, cudaStream_t st) 
     return cudaGetLastError();
 }
 
+static bool func_ready(fd_handle* h, const void* fn, size_t smem) {  // shared-memory opt-in done for (kernel, size)?
+    for (const auto& c : h->launch_cfg)
+        if (c.fn == fn && c.smem == smem) return true;
+    return false;
+}
+
+// merged: both variants in one launch (their table pools must not overlap: RowArgs::big_tabs / big2_tabs);
+// otherwise one launch each, medium first (the pools may then be the same memory -- fd_transform_noalloc's fixed array)
 template <int MODE, bool CLEAN>
-static cudaError_t launch_wide(fd_handle* h, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st) {
+static cudaError_t launch_wide(fd_handle* h, const RowArgs& a, int med_ctas, int big_workers, bool merged, cudaStream_t st) {
     const size_t smem_med = a.m.sw_smem_bytes() + (size_t)MED_WARPS * sizeof(WarpSmem<9>);
     const size_t smem_big = a.m.sw_smem_bytes() + sizeof(WarpSmem<9>);
+    if (merged) {
+        auto kern = k_wide<MODE, CLEAN>;
+        if (!func_ready(h, (const void*)kern, smem_med)) {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_med);
+            if (e != cudaSuccess) return e;
+            h->launch_cfg.push_back({(const void*)kern, smem_med, 1});
+        }
+        kern<<<med_ctas + big_workers, 32 * MED_WARPS, smem_med, st>>>(a, med_ctas, big_workers);
+        h->launches += 1;
+        return cudaGetLastError();
+    }
     auto kmed = k_rows<MODE, CLEAN, 1, 9>;
     auto kbig = k_rows<MODE, CLEAN, 2, 9>;
-    cudaError_t e = cudaFuncSetAttribute(kmed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_med);
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(kbig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_big);
-    if (e != cudaSuccess) return e;
+    if (!func_ready(h, (const void*)kmed, smem_med)) {
+        cudaError_t e = cudaFuncSetAttribute(kmed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_med);
+        if (e != cudaSuccess) return e;
+        h->launch_cfg.push_back({(const void*)kmed, smem_med, 1});
+    }
+    if (!func_ready(h, (const void*)kbig, smem_big)) {
+        cudaError_t e = cudaFuncSetAttribute(kbig, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_big);
+        if (e != cudaSuccess) return e;
+        h->launch_cfg.push_back({(const void*)kbig, smem_big, 1});
+    }
     kmed<<<med_ctas, 32 * MED_WARPS, smem_med, st>>>(a);
     kbig<<<big_workers, 32, smem_big, st>>>(a);
     h->launches += 2;
     return cudaGetLastError();
 }
 
-// Micro-batches always take the 512-slot shape (fewer deferrals, lower latency).  Large batches let the device
-// choose: both shapes are launched and the one that was not picked exits at once.
-void launch_pick_shape(fd_handle* h, const RowArgs& a, float keep, cudaStream_t st) {
-    k_pick_shape<<<1, 1, 0, st>>>(a.offs, a.n_rows, keep, a.ctrl);
-    h->launches += 1;
-}
-
 // Main kernel first (fd_main.cu; CountVectorizer.fit keeps the kernel of this file, whose global term table must see
 // every token exactly once), then the two wide-table kernels over the dialogues it deferred.
 template <int MODE, bool CLEAN>
-static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a0, int med_ctas, int big_workers, cudaStream_t st) {
+static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a0, int med_ctas, int big_workers, bool merged, cudaStream_t st) {
     cudaError_t e;
     if (MODE == MODE_FIT) {
         // micro-batches always take the 512-slot shape; large batches let the device choose: both shapes are launched
@@ -908,23 +939,23 @@ static cudaError_t launch_mode_workers(fd_handle* h, const RowArgs& a0, int med_
         RowArgs a = a0;
         if (a.n_rows >= ROWS_FOR_SMALL_TABLES) {
             a.pick_shape = 1;
-            launch_pick_shape(h, a, 1.0f, st);
+            a.pick_keep = 1.0f;
             e = launch_main<MODE_FIT, CLEAN, 8>(h, a, st);
             if (e != cudaSuccess) return e;
         }
         e = launch_main<MODE_FIT, CLEAN, 9>(h, a, st);
         if (e != cudaSuccess) return e;
-        return launch_wide<MODE_FIT, CLEAN>(h, a, med_ctas, big_workers, st);
+        return launch_wide<MODE_FIT, CLEAN>(h, a, med_ctas, big_workers, merged, st);
     }
     e = launch_main_rows(h, MODE, a0, st);
     if (e != cudaSuccess) return e;
-    return launch_wide<MODE, CLEAN>(h, a0, med_ctas, big_workers, st);
+    return launch_wide<MODE, CLEAN>(h, a0, med_ctas, big_workers, merged, st);
 }
 
 // the caller provides a.big_tabs with wide_pool_slots(med_ctas, big_workers) slots
-cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st) {
+cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int med_ctas, int big_workers, bool merged, cudaStream_t st) {
     const bool c = (a.flags & FD_FLAG_CLEAN) != 0;
-#define FD_DISPATCH(M) return c ? launch_mode_workers<M, true>(h, a, med_ctas, big_workers, st) : launch_mode_workers<M, false>(h, a, med_ctas, big_workers, st)
+#define FD_DISPATCH(M) return c ? launch_mode_workers<M, true>(h, a, med_ctas, big_workers, merged, st) : launch_mode_workers<M, false>(h, a, med_ctas, big_workers, merged, st)
     switch (mode) {
         case MODE_CSR: FD_DISPATCH(MODE_CSR);
         case MODE_LINEAR: FD_DISPATCH(MODE_LINEAR);
@@ -938,7 +969,7 @@ cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int me
 }
 
 cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st) {
-    return launch_rows_workers(h, mode, a, MED_CTAS, BIG_WORKERS, st);
+    return launch_rows_workers(h, mode, a, MED_CTAS, BIG_WORKERS, true, st);
 }
 
 cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, unsigned long long* tmp,

@@ -25,15 +25,23 @@ constexpr int MED_LOG2 = 12;
 constexpr int MED_WARPS = 8;
 constexpr int MED_CTAS = 296;
 constexpr int BIG_LOG2 = 16;
-constexpr int BIG_WORKERS = 148;
+constexpr int BIG_WORKERS = 48;   // (the two variants run side by side in one launch: each has its own table pool)
 // Micro-batch / long-dialogue shape (TL = 9): a warp whose shared-memory table fills up carries on in its OWN 2^MED_LOG2-slot
 // table in global memory (the entries move over, the dialogue is not restarted); only dialogues that outgrow that one as
 // well are deferred.  One table per warp of the grid, SPILL_WARPS at most.
 constexpr int SPILL_WARPS = 160 * 3 * 8;
 constexpr size_t SPILL_SLOTS = (size_t)SPILL_WARPS << MED_LOG2;
+constexpr size_t med_pool_slots(int med_ctas) { return (size_t)med_ctas * MED_WARPS << MED_LOG2; }
+constexpr size_t big_pool_slots(int big_workers) { return (size_t)big_workers << BIG_LOG2; }
+// one pool for both when they run one after the other (fd_transform_noalloc), two disjoint pools when they run together
 constexpr size_t wide_pool_slots(int med_ctas, int big_workers) {
-    return ((size_t)med_ctas * MED_WARPS << MED_LOG2) > ((size_t)big_workers << BIG_LOG2) ? ((size_t)med_ctas * MED_WARPS << MED_LOG2)
-                                                                                         : ((size_t)big_workers << BIG_LOG2);
+    return med_pool_slots(med_ctas) > big_pool_slots(big_workers) ? med_pool_slots(med_ctas) : big_pool_slots(big_workers);
+}
+
+// the kernel shape for a large batch, from the mean dialogue length (device side: every CTA of both shapes evaluates it)
+__host__ __device__ inline int shape_for(long long total_bytes, long long n_rows, float keep) {
+    const long long mean = total_bytes / (n_rows > 0 ? n_rows : 1);
+    return (float)mean * keep <= (float)MEAN_BYTES_FOR_SMALL_TABLES ? 8 : 9;
 }
 
 enum Mode { MODE_CSR = 0, MODE_LINEAR = 1, MODE_DT = 2, MODE_RF = 3, MODE_GBT = 4, MODE_FIT = 5 };
@@ -57,8 +65,11 @@ struct RowArgs {
     Ctrl* ctrl;
     long long* big_rows;
     long long big_cap;
-    int pick_shape;  // 1: both main-kernel shapes are launched and ctrl->shape says which one runs
-    unsigned long long* big_tabs;
+    int pick_shape;  // 1: both main-kernel shapes are launched and each decides from the mean dialogue length whether it runs
+    float pick_keep; // ... scaled by the fraction of a dialogue's terms that reach the count table (sparse LogisticRegression)
+    long long host_bytes;  // total text bytes when the caller knows them on the host (the shape is then picked there), else -1
+    unsigned long long* big_tabs;    // table pool of the medium wide-table variant
+    unsigned long long* big2_tabs;   // ... of the large one (may equal big_tabs when the two variants run one after the other)
     unsigned long long* spill_tabs;  // SPILL_SLOTS slots, or nullptr (no spilling: overflowing dialogues are deferred)
     // featurize outputs (staging)
     int32_t* row_nnz;
@@ -80,8 +91,7 @@ struct RowArgs {
 
 cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st);
 cudaError_t launch_main_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st);  // fd_main.cu
-void launch_pick_shape(fd_handle* h, const RowArgs& a, float keep, cudaStream_t st);
-cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int med_ctas, int big_workers, cudaStream_t st);
+cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int med_ctas, int big_workers, bool merged, cudaStream_t st);
 cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, unsigned long long* tmp,
                                 long long n_rows, long long* bsum, long long* rowptr, int32_t* out_idx, double* out_val,
                                 bool scan_only, cudaStream_t st);
