@@ -498,6 +498,8 @@ int fd_set_hashing(fd_handle* h, int32_t num_features, int32_t binary) {
     m.mod_magic = m.mod_pow2 ? 0u : (uint32_t)((1ULL << 32) / (uint64_t)num_features);
     m.mod_r32 = (uint32_t)((1ULL << 32) % (uint64_t)num_features);
     m.empty_idx = nonneg_mod_host(murmur3_host(nullptr, 0), num_features);
+    m.csr_list = num_features <= (1 << 22) ? 1 : 0;
+    m.bin_mul = num_features > 256 ? (uint32_t)((1ULL << 40) / (uint64_t)num_features) : 0u;
     if (m.vocab_tab) cudaFree(m.vocab_tab);
     if (m.vocab_words) cudaFree(m.vocab_words);
     if (m.vocab_pool) cudaFree(m.vocab_pool);
@@ -566,6 +568,8 @@ int fd_set_vocabulary(fd_handle* h, const uint8_t* words, const int32_t* offs, i
     if (!rc) rc = upload(h, &m.vocab_pool, pool.data(), pool.size());
     if (rc) return rc;
     m.vocab_cap = cap;
+    m.csr_list = 0;  // (vocabulary indices are not evenly spread: the count-table path)
+    m.bin_mul = 0;
     drop_feature_space(h, n_words, true);
     m.num_features = n_words;
     m.binary = binary ? 1 : 0;

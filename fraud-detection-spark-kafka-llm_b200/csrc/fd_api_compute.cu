@@ -136,11 +136,12 @@ int fd_featurize_begin(fd_handle* h, const uint8_t* text_dev, const int64_t* off
                        (1 << BIG_LOG2) * 3 / 4);
     }
     h->feat_rows = n_rows;
+    h->feat_unsorted = (int64_t)c.big_count + (int64_t)c.big2_count;  // dialogues the wide-table kernel staged (not ordered)
     h->feat_nnz = (int64_t)c.tmp_cursor;
     *nnz_host = h->feat_nnz;
     // exclusive scan of per-dialogue nnz (block sums now; row pointers in finish)
     FD_CUDA(h, launch_csr_assembly(h, reinterpret_cast<int32_t*>(h->ws + h->off_nnz), nullptr, nullptr, n_rows,
-                                   reinterpret_cast<long long*>(h->ws + h->off_bsum), nullptr, nullptr, nullptr, true, st));
+                                   reinterpret_cast<long long*>(h->ws + h->off_bsum), nullptr, nullptr, nullptr, true, 0, st));
     return FD_OK;
 }
 
@@ -161,7 +162,7 @@ int fd_featurize_finish(fd_handle* h, int64_t* out_rowptr_dev, int32_t* out_idx_
                                    reinterpret_cast<long long*>(h->ws + h->off_tmpoff),
                                    reinterpret_cast<unsigned long long*>(h->ws + h->off_tmp), h->feat_rows,
                                    reinterpret_cast<long long*>(h->ws + h->off_bsum), (long long*)out_rowptr_dev, out_idx_dev,
-                                   out_val_dev, false, st));
+                                   out_val_dev, false, h->feat_unsorted, st));
     return FD_OK;
 }
 

@@ -67,6 +67,10 @@ struct Model {
     uint32_t mod_magic = 0;  // floor(2^32 / num_features)
     uint32_t mod_r32 = 0;    // 2^32 mod num_features
     int mod_pow2 = 0;
+    // featurize through a token list ordered by a counting sort (fd_main.cu csr_sorted_emit): hashing trick with
+    // numFeatures <= 2^22; bin_mul = floor(2^40 / numFeatures) maps a bucket to one of 256 bins (0: the bucket itself)
+    int csr_list = 0;
+    uint32_t bin_mul = 0;
     // idf
     double* idf = nullptr;
     // classifier
@@ -128,6 +132,7 @@ struct fd_handle {
     // featurize state between begin/finish
     int64_t feat_rows = -1;
     int64_t feat_nnz = 0;
+    int64_t feat_unsorted = 0;
     size_t off_nnz = 0, off_tmpoff = 0, off_tmp = 0, off_bsum = 0;
     int64_t tmp_cap = 0;
     int64_t launches = 0;

@@ -161,6 +161,132 @@ __device__ __forceinline__ uint32_t rotl_c(uint32_t x) {
 }
 __device__ __forceinline__ uint32_t mmk(uint32_t k) { return rotl_c<15>(k * 0xcc9e2d51u) * 0x1b873593u; }
 
+__device__ __forceinline__ uint32_t atoms_add_u32(uint32_t a, uint32_t v) {  // returns the old value
+    uint32_t old;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(a), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ void sts_v4(uint32_t a, uint4 v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// featurize with a TOKEN LIST (Model::csr_list: hashing trick, numFeatures <= 2^22): pass B only appends the bucket of
+// every surviving token to a list in shared memory; at the end of the dialogue the list is ordered by a counting sort
+// (256 bins by the bucket's top bits -- hashed buckets are evenly spread --, a shared-memory atomic gives every token its
+// arrival rank inside its bin, a scan the bins' start positions, tokens that share a bin are placed by counting the bin's
+// smaller keys and earlier equals), runs of equal buckets become (bucket, count) entries, and the dialogue's row goes to
+// the staging buffer already ORDERED (flagged in row_tmpoff), so that k_gather_csr only forms the values.
+// listA: n keys (u32); binsA: 256 words + later the run starts (u16); outA: room for n keys.  Returns the row's nnz.
+constexpr long long ROW_SORTED = 1LL << 62;  // flag in row_tmpoff
+constexpr int CSR_LIST_MAX = 544;            // tokens a list may hold (the ordered copy lives in the token-list area)
+template <bool POW2>
+__device__ __forceinline__ uint32_t bucket_bin(const Model& m, uint32_t key, int bin_shift) {
+    if (POW2) return key >> bin_shift;
+    return m.bin_mul ? __umulhi(key, m.bin_mul) : key;
+}
+template <bool POW2>
+__device__ int csr_sorted_emit(const RowArgs& a, uint32_t listA, int n, uint32_t binsA, uint32_t outA, long long row, int lane, int bin_shift) {
+    constexpr uint32_t FULL = 0xFFFFFFFFu;
+    const Model& m = a.m;
+    const uint32_t below = (1u << lane) - 1u;
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    sts_v4(binsA + 32u * (uint32_t)lane, z);
+    sts_v4(binsA + 32u * (uint32_t)lane + 16u, z);
+    __syncwarp();
+    for (int e = lane; e < n; e += 32) {  // arrival rank inside the bin, kept in the key's top 10 bits
+        const uint32_t key = lds_u32(listA + 4u * (uint32_t)e);
+        const uint32_t r = atoms_add_u32(binsA + 4u * bucket_bin<POW2>(m, key, bin_shift), 1u);
+        sts_u32(listA + 4u * (uint32_t)e, key | (r << 22));
+    }
+    __syncwarp();
+    {   // exclusive scan of the 256 bin sizes: 8 consecutive bins per lane
+        const uint4 p = lds_v4(binsA + 32u * (uint32_t)lane), q = lds_v4(binsA + 32u * (uint32_t)lane + 16u);
+        const uint32_t tot = p.x + p.y + p.z + p.w + q.x + q.y + q.z + q.w;
+        uint32_t inc = tot;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t v = __shfl_up_sync(FULL, inc, d);
+            if (lane >= d) inc += v;
+        }
+        uint32_t run = inc - tot;
+        uint4 o0, o1;
+        o0.x = run; run += p.x;
+        o0.y = run; run += p.y;
+        o0.z = run; run += p.z;
+        o0.w = run; run += p.w;
+        o1.x = run; run += q.x;
+        o1.y = run; run += q.y;
+        o1.z = run; run += q.z;
+        o1.w = run;
+        sts_v4(binsA + 32u * (uint32_t)lane, o0);
+        sts_v4(binsA + 32u * (uint32_t)lane + 16u, o1);
+    }
+    __syncwarp();
+    for (int e = lane; e < n; e += 32) {  // into the bins (arrival order inside a bin)
+        const uint32_t w = lds_u32(listA + 4u * (uint32_t)e);
+        const uint32_t key = w & 0x3FFFFFu;
+        sts_u32(outA + 4u * (lds_u32(binsA + 4u * bucket_bin<POW2>(m, key, bin_shift)) + (w >> 22)), key);
+    }
+    __syncwarp();
+    // A bin usually holds the repetitions of ONE bucket (then its tokens already sit together): bins with two or more
+    // different buckets are marked (bit 31 of the bin's start), and only their tokens look for their final place
+    for (int e = lane; e < n; e += 32) {
+        const uint32_t key = lds_u32(outA + 4u * (uint32_t)e);
+        const uint32_t ba = binsA + 4u * bucket_bin<POW2>(m, key, bin_shift);
+        if (lds_u32(outA + 4u * (lds_u32(ba) & 0xFFFFu)) != key) asm volatile("red.shared.or.b32 [%0], %1;" ::"r"(ba), "r"(0x80000000u) : "memory");
+    }
+    __syncwarp();
+    for (int e = lane; e < n; e += 32) {  // final place: smaller keys of the bin first, equal keys in position order
+        const uint32_t key = lds_u32(outA + 4u * (uint32_t)e);
+        const uint32_t bin = bucket_bin<POW2>(m, key, bin_shift);
+        const uint32_t b0 = lds_u32(binsA + 4u * bin);
+        uint32_t pos = (uint32_t)e;
+        if (b0 >> 31) {
+            const uint32_t s0 = b0 & 0xFFFFu, s1 = bin == 255u ? (uint32_t)n : (lds_u32(binsA + 4u * bin + 4u) & 0xFFFFu);
+            pos = s0;
+            for (uint32_t j = s0; j < s1; ++j) {
+                const uint32_t kj = lds_u32(outA + 4u * j);
+                pos += (kj < key || (kj == key && j < (uint32_t)e)) ? 1u : 0u;
+            }
+        }
+        sts_u32(listA + 4u * pos, key);
+    }
+    __syncwarp();
+    // runs of equal buckets: start[d] = first position of the d-th distinct bucket (u16, over the bins' area)
+    uint32_t D = 0;
+    for (int c = 0; c < n; c += 32) {
+        const int e = c + lane;
+        bool head = false;
+        if (e < n) {
+            const uint32_t key = lds_u32(listA + 4u * (uint32_t)e);
+            head = e == 0 || lds_u32(listA + 4u * (uint32_t)e - 4u) != key;
+        }
+        const uint32_t bal = __ballot_sync(FULL, head);
+        if (head) sts_u16(binsA + 2u * (D + (uint32_t)__popc(bal & below)), (uint32_t)e);
+        D += (uint32_t)__popc(bal);
+    }
+    if (lane == 0) sts_u16(binsA + 2u * D, (uint32_t)n);
+    __syncwarp();
+    unsigned long long pos = 0;
+    if (lane == 0) pos = atomicAdd(&a.ctrl->tmp_cursor, (unsigned long long)D);
+    pos = __shfl_sync(FULL, pos, 0);
+    const bool fits = (long long)(pos + D) <= a.tmp_cap;
+    if (!fits && lane == 0) a.ctrl->tmp_overflow = 1u;
+    unsigned long long* dst = a.tmp + pos;
+    if (fits) {
+        for (uint32_t d = (uint32_t)lane; d < D; d += 32u) {
+            const uint32_t s0 = lds_u16(binsA + 2u * d), s1 = lds_u16(binsA + 2u * d + 2u);
+            const uint32_t key = lds_u32(listA + 4u * s0);
+            dst[d] = ((unsigned long long)key << 32) | (unsigned long long)(m.binary ? 1u : s1 - s0);
+        }
+    }
+    if (lane == 0) {
+        a.row_nnz[row] = (int32_t)D;
+        a.row_tmpoff[row] = (long long)pos | ROW_SORTED;
+    }
+    return (int)D;
+}
+
 // MODE: what happens to the counted terms (fd_rows.cuh); CLEAN: FD_FLAG_CLEAN; TL: log2 of the count-table slots and the
 // CTA shape (row_warps); DTS: small-decision-tree path (MODE_DT with Model::dt_heap_on, hashing trick) -- per-warp counters
 // instead of a count table, nothing is ever deferred for size; 2 = some split feature is also a stop word's bucket;
@@ -223,6 +349,9 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
     const uint8_t* text = a.text;
     const bool binary = m.binary != 0;
     const uint32_t fmask = (uint32_t)(m.num_features - 1);
+    const bool csr_list = MODE == MODE_CSR && m.csr_list != 0;      // featurize: token list instead of a count table
+    const int bin_shift = max(__popc(fmask) - 8, 0);                // (POW2) bucket -> one of 256 bins
+    const int list_cap = min(CSR_LIST_MAX, (8 << TL) / 4);          // keys the table area holds
     unsigned long long* tab = stab;  // TL == 9: may move to the warp's wide table in global memory
     int TLOG2 = TL;
     // DTS: this lane's split node (heap order) and the output column it stores
@@ -416,8 +545,17 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                     bool isnew = false;
                     const uint32_t fi = m.empty_idx;
                     const bool seen = MODE == MODE_CSR || !m.filt_on || ((__ldg(&m.filt[fi >> 5].x) >> (fi & 31)) & 1u);
-                    if (lane == 0 && seen) isnew = tab_insert(tab, TLOG2, fi, pend, binary);
-                    D += __popc(__ballot_sync(FULL, isnew));
+                    if (csr_list) {
+                        if (D + pend > (uint32_t)list_cap) {
+                            big = true;
+                        } else {
+                            for (uint32_t i = (uint32_t)lane; i < pend; i += 32u) sts_u32(cntA + 4u * (D + i), fi);
+                            D += pend;
+                        }
+                    } else {
+                        if (lane == 0 && seen) isnew = tab_insert(tab, TLOG2, fi, pend, binary);
+                        D += __popc(__ballot_sync(FULL, isnew));
+                    }
                 }
             }
             pend = 0;
@@ -428,7 +566,12 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
         auto pass_b = [&](auto plain_tag) {
             constexpr bool PLAIN = decltype(plain_tag)::value;
             for (int t0 = 0; t0 < Tc; t0 += 32) {
-                if (!DTS && D + 32u > (3u << TLOG2) / 4u) {  // keep the table at most 3/4 full
+                if (csr_list) {
+                    if (D + 32u > (uint32_t)list_cap) {  // the list is full: the wide-table kernel takes the dialogue
+                        big = true;
+                        break;
+                    }
+                } else if (!DTS && D + 32u > (3u << TLOG2) / 4u) {  // keep the table at most 3/4 full
                     const long long gw = (long long)blockIdx.x * ROW_WARPS + warp;
                     if (TL == 9 && tab == stab && a.spill_tabs != nullptr && gw < SPILL_WARPS) {
                         // carry on in this warp's own wide table: clear it, move the entries over, switch
@@ -561,6 +704,12 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                         ins = ins && !stop_probe(m, swt, sww, h, n, b0, b1, b2, rb, S.lmask, s, e, valid && !empty);
                     }
                     bool isnew = false;
+                    if (csr_list) {  // append the bucket; the end of the dialogue orders and counts the list
+                        const uint32_t bal = __ballot_sync(FULL, ins);
+                        if (ins) sts_u32(cntA + 4u * (D + (uint32_t)__popc(bal & ((1u << lane) - 1u))), fi);
+                        D += (uint32_t)__popc(bal);
+                        continue;
+                    }
                     if (TL == 8 || tab == stab) {  // (named so that the common case keeps shared-memory atomics)
                         if (ins) isnew = tab_insert(stab, TL, fi, 1u, binary);
                     } else {
@@ -587,8 +736,13 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                 } else {
                     bool isnew = false;
                     const bool seen = MODE == MODE_CSR || !m.filt_on || ((__ldg(&m.filt[fi >> 5].x) >> (fi & 31)) & 1u);
-                    if (lane == 0 && seen) isnew = tab_insert(tab, TLOG2, fi, 1u, binary);
-                    D += __popc(__ballot_sync(FULL, isnew));
+                    if (csr_list) {
+                        if (lane == 0) sts_u32(cntA + 4u * D, fi);  // (D == 0 here: nothing was kept)
+                        D += 1u;
+                    } else {
+                        if (lane == 0 && seen) isnew = tab_insert(tab, TLOG2, fi, 1u, binary);
+                        D += __popc(__ballot_sync(FULL, isnew));
+                    }
                 }
             }
             __syncwarp();
@@ -618,6 +772,8 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                 for (int d = 0; d < 5; ++d) p = 2 * p + 1 + (int)((bits >> p) & 1u);
                 if (lane < 5) outp[(long long)row * ostride] = dto[(p - 31) * 5 + lane];
                 sts_u32(ca, 0u);  // (only split-feature counters are ever touched; each is some lane's)
+            } else if (csr_list) {
+                csr_sorted_emit<POW2>(a, cntA, (int)D, rbA, tokA, row, lane, bin_shift);
             } else if (TL == 8 || tab == stab) {
                 row_epilogue<MODE>(a, reinterpret_cast<double*>(S.tok), reinterpret_cast<double*>(rb), true, stab, TL, row, (int)D, lane);
             } else {
@@ -630,8 +786,10 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                     tab = stab;
                     TLOG2 = TL;
                 }
-                const uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);  // count = 0, key = EMPTY
-                for (int i = lane; i < (1 << TL) / 2; i += 32) reinterpret_cast<uint4*>(stab)[i] = ff;
+                if (!csr_list) {
+                    const uint4 ff = make_uint4(0u, ~0u, 0u, ~0u);  // count = 0, key = EMPTY
+                    for (int i = lane; i < (1 << TL) / 2; i += 32) reinterpret_cast<uint4*>(stab)[i] = ff;
+                }
             }
             D = 0;
             pend = 0;

@@ -790,6 +790,27 @@ __device__ __forceinline__ void gather_counted_k(const unsigned long long* __res
     __syncwarp();
 }
 
+// rows the dialogue kernel staged already ordered (token-list path, flagged in tmpoff): only the values are formed.
+// No shared memory and few registers, so 64 warps per SM hide the two dependent loads (entry, idf) of a row.
+__global__ void __launch_bounds__(256) k_gather_copy(const unsigned long long* __restrict__ tmp, const long long* __restrict__ tmpoff,
+                                                     const long long* __restrict__ rowptr, long long n_rows, const double* __restrict__ idf,
+                                                     int32_t* __restrict__ out_idx, double* __restrict__ out_val) {
+    const int lane = threadIdx.x & 31;
+    const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+    for (long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n_rows; r += nwarps) {
+        const long long toff = tmpoff[r];
+        if (!(toff & (1LL << 62))) continue;
+        const long long o = rowptr[r], n = rowptr[r + 1] - o, t = toff & ~(1LL << 62);
+        for (long long i = lane; i < n; i += 32) {
+            const unsigned long long e = tmp[t + i];
+            const uint32_t idx = (uint32_t)(e >> 32);
+            const double c = (double)(uint32_t)e;
+            out_idx[o + i] = (int32_t)idx;
+            out_val[o + i] = idf ? __dmul_rn(c, __ldg(idf + idx)) : c;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(32 * GATHER_WARPS, 4) k_gather_csr(unsigned long long* __restrict__ tmp, const long long* __restrict__ tmpoff,
                                                                      const long long* __restrict__ rowptr, long long n_rows,
                                                                      const double* __restrict__ idf, int small_keys, int even_keys,
@@ -813,9 +834,11 @@ __global__ void __launch_bounds__(32 * GATHER_WARPS, 4) k_gather_csr(unsigned lo
       const int nr = (int)(n_rows - r0 < rpw ? n_rows - r0 : rpw);
       for (int k = 0; k < nr; ++k) {
         const long long o = __shfl_sync(0xFFFFFFFFu, my_o, k), nl = __shfl_sync(0xFFFFFFFFu, my_e, k) - o;
-        unsigned long long* src = tmp + __shfl_sync(0xFFFFFFFFu, my_t, k);
+        const long long toff = __shfl_sync(0xFFFFFFFFu, my_t, k);
+        unsigned long long* src = tmp + (toff & ~(1LL << 62));
         int32_t* oi = out_idx + o;
         double* ov = out_val + o;
+        if (toff & (1LL << 62)) continue;  // staged already ordered: k_gather_copy formed this row
         if (even_keys && nl <= 256) {
             const int n = (int)nl;
             if (n <= 32) gather_counted_k<1>(src, n, keys, fkeys, cnts, bins, bin_mul, lane, idf, oi, ov);
@@ -974,7 +997,7 @@ cudaError_t launch_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t s
 
 cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, unsigned long long* tmp,
                                 long long n_rows, long long* bsum, long long* rowptr, int32_t* out_idx, double* out_val,
-                                bool scan_only, cudaStream_t st) {
+                                bool scan_only, long long unsorted_rows, cudaStream_t st) {
     const int nb = (int)((n_rows + SCAN_BLOCK - 1) / SCAN_BLOCK);
     if (scan_only) {
         k_scan_block_sums<<<nb, SCAN_BLOCK, 0, st>>>(nnz, n_rows, bsum);
@@ -983,15 +1006,25 @@ cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long lon
         return cudaGetLastError();
     }
     k_scan_rowptr<<<nb, SCAN_BLOCK, 0, st>>>(nnz, n_rows, bsum, rowptr);
-    const int rpw = (int)std::min<long long>(32, std::max<long long>(1, n_rows / 8192));  // dialogues per warp and round
-    long long g = (n_rows + rpw * GATHER_WARPS - 1) / (rpw * GATHER_WARPS);
-    if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
-    // hashed buckets are evenly spread (counting sort); vocabulary indices are not (frequent terms have the low ones)
-    const int even_keys = h->m.vocab_cap ? 0 : 1;
-    const uint32_t bin_mul = h->m.num_features > 256 ? (uint32_t)((1ULL << 40) / (uint64_t)h->m.num_features) : 0u;
-    k_gather_csr<<<(unsigned)g, 32 * GATHER_WARPS, 0, st>>>(tmp, tmpoff, rowptr, n_rows, h->m.idf, h->m.num_features <= (1 << 23) ? 1 : 0, even_keys,
-                                                       bin_mul, rpw, out_idx, out_val);
-    h->launches += 2;
+    // rows staged in order (token-list path) are copied; the others (count-table path, deferred dialogues) are ordered here
+    if (h->m.csr_list) {
+        long long gc = (n_rows + 7) / 8;
+        if (gc > (long long)h->sm_count * 8) gc = (long long)h->sm_count * 8;
+        k_gather_copy<<<(unsigned)gc, 256, 0, st>>>(tmp, tmpoff, rowptr, n_rows, h->m.idf, out_idx, out_val);
+        h->launches += 1;
+    }
+    if (!h->m.csr_list || unsorted_rows > 0) {
+        const int rpw = (int)std::min<long long>(32, std::max<long long>(1, n_rows / 8192));  // dialogues per warp and round
+        long long g = (n_rows + rpw * GATHER_WARPS - 1) / (rpw * GATHER_WARPS);
+        if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
+        // hashed buckets are evenly spread (counting sort); vocabulary indices are not (frequent terms have the low ones)
+        const int even_keys = h->m.vocab_cap ? 0 : 1;
+        const uint32_t bin_mul = h->m.num_features > 256 ? (uint32_t)((1ULL << 40) / (uint64_t)h->m.num_features) : 0u;
+        k_gather_csr<<<(unsigned)g, 32 * GATHER_WARPS, 0, st>>>(tmp, tmpoff, rowptr, n_rows, h->m.idf, h->m.num_features <= (1 << 23) ? 1 : 0, even_keys,
+                                                           bin_mul, rpw, out_idx, out_val);
+        h->launches += 1;
+    }
+    h->launches += 1;  // (the row-pointer scan)
     return cudaGetLastError();
 }
 

@@ -94,7 +94,7 @@ cudaError_t launch_main_rows(fd_handle* h, int mode, const RowArgs& a, cudaStrea
 cudaError_t launch_rows_workers(fd_handle* h, int mode, const RowArgs& a, int med_ctas, int big_workers, bool merged, cudaStream_t st);
 cudaError_t launch_csr_assembly(fd_handle* h, const int32_t* nnz, const long long* tmpoff, unsigned long long* tmp,
                                 long long n_rows, long long* bsum, long long* rowptr, int32_t* out_idx, double* out_val,
-                                bool scan_only, cudaStream_t st);
+                                bool scan_only, long long unsorted_rows, cudaStream_t st);
 cudaError_t launch_score_csr(fd_handle* h, const int64_t* rowptr, const int32_t* idx, const double* val, long long n_rows,
                              double* pred, double* prob, double* raw, cudaStream_t st);
 
