@@ -619,6 +619,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                 }
                 // ---- murmur3 of a contiguous token, first 12 bytes straight-line
                 uint32_t b0, b1, b2, h;
+                bool any_empty = false;  // (warp-uniform; plain windows only)
                 {
                     const uint32_t pa = rbA + (uint32_t)p0;
                     const uint32_t wa = pa & ~3u;
@@ -636,7 +637,8 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                     h = nn >= 8 ? rotl_c<13>(t) * 5u + 0xe6546b64u : t;
                     t = h ^ mmk(b2);
                     h = nn >= 12 ? rotl_c<13>(t) * 5u + 0xe6546b64u : t;
-                    if (__any_sync(FULL, nn > 12)) {
+                    // one vote covers both rare cases of a plain window: a token longer than 12 bytes, an empty token
+                    if (__any_sync(FULL, nn > 12 || (PLAIN && valid && empty))) {
                         if (nn > 12) {
                             uint32_t prev = w3;
                             for (int i = 3; nn > 4 * i; ++i) {
@@ -647,6 +649,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                                 h = r >= 4 ? mm_h(h, mm_k(k)) : h ^ mm_k(k & low_mask(8 * r));
                             }
                         }
+                        if (PLAIN) any_empty = __any_sync(FULL, valid && empty);
                     }
                     h = mm_fmix(h, (uint32_t)nn);
                 }
@@ -666,7 +669,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                 }
                 // ---- empty tokens count when a kept byte follows somewhere in the dialogue (Java's split drops trailing ones)
                 bool ins = valid;
-                if (__any_sync(FULL, valid && empty)) {
+                if (PLAIN ? any_empty : __any_sync(FULL, valid && empty)) {
                     const bool interior = empty && s <= last_letter;
                     ins = valid && (empty ? (interior && !m.drop_empty) : true);
                     pend += __popc(__ballot_sync(FULL, valid && empty && !interior));
