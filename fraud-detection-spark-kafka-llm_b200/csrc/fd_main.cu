@@ -161,6 +161,37 @@ __device__ __forceinline__ uint32_t rotl_c(uint32_t x) {
 }
 __device__ __forceinline__ uint32_t mmk(uint32_t k) { return rotl_c<15>(k * 0xcc9e2d51u) * 0x1b873593u; }
 
+// stop_probe with the tables addressed by 32-bit shared address (swtA: slots, swwA: 16-byte word records): the hot form
+// for featurize and dense classifiers, where every token is probed.  The record of slot value `id` sits at
+// swwA + 16 (id - 1); id = 0 (no word) reads the 16 bytes before the records -- valid shared memory -- and is masked out.
+__device__ __forceinline__ bool stop_probe_s(const Model& m, uint32_t swtA, uint32_t swwA, uint32_t h, uint32_t n, uint32_t b0, uint32_t b1,
+                                             uint32_t b2, const uint8_t* rb, const uint32_t* lmask, int s, int e, bool cand) {
+    bool stop = false;
+    if (m.sw_perfect) {
+        const uint32_t id = lds_u16(swtA + 2u * ((h * m.sw_mul) >> m.sw_shift));
+        const uint4 w = lds_v4(swwA + 16u * id - 16u);
+        const bool c = cand && id != 0u;
+        stop = c && (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
+        if (c && w.x == (n | 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, lmask, s, e);
+    } else if (m.sw_cap) {
+        const uint32_t swmask = (uint32_t)m.sw_cap - 1u;
+        const uint32_t e1 = lds_u32(swtA + 4u * (h & swmask)), e2 = lds_u32(swtA + 4u * ((h >> 10) & swmask));
+        const bool m1 = e1 != 0u && ((e1 ^ h) >> 16) == 0u, m2 = e2 != 0u && ((e2 ^ h) >> 16) == 0u;
+        if (cand && (m1 || m2)) {
+            const uint32_t ent = m1 ? e1 : e2;
+            uint4 w = lds_v4(swwA + 16u * (ent & 0xFFFFu) - 16u);
+            stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
+            if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, lmask, s, e);
+            if (!stop && m1 && m2) {  // fingerprint collision in the first slot: look at the second
+                w = lds_v4(swwA + 16u * (e2 & 0xFFFFu) - 16u);
+                stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
+                if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, lmask, s, e);
+            }
+        }
+    }
+    return stop;
+}
+
 __device__ __forceinline__ uint32_t atoms_add_u32(uint32_t a, uint32_t v) {  // returns the old value
     uint32_t old;
     asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(old) : "r"(a), "r"(v) : "memory");
@@ -315,6 +346,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
     uint32_t lutA;  // (opaque to the compiler, so that it stays in a register instead of being rebuilt at every use)
     asm volatile("mov.u32 %0, %1;" : "=r"(lutA) : "r"(smem_u32(smem_raw)));
     const uint32_t dtkA = lutA + LUT_BYTES;
+    const uint32_t swtA = lutA + LUT_BYTES, swwA = swtA + (uint32_t)m.sw_tab_bytes();  // !DTS: the stop-word tables
     const uint32_t rawA = smem_u32(wmem);
     const uint32_t tokA = rawA + (uint32_t)offsetof(MainWarp, tok);
     const uint32_t cntA = rawA + (uint32_t)sizeof(MainWarp);
@@ -701,10 +733,10 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                         ins = ins && ((fw.x >> (fi & 31)) & 1u);           // can the classifier see this feature at all?
                         const bool chk = ins && !empty && ((fw.y >> (fi & 31)) & 1u);
                         if (__any_sync(FULL, chk)) {                       // ... and a stop word maps to it: is the token one?
-                            if (chk) ins = !stop_probe(m, swt, sww, h, n, b0, b1, b2, rb, S.lmask, s, e, true);
+                            if (chk) ins = !stop_probe_s(m, swtA, swwA, h, n, b0, b1, b2, rb, S.lmask, s, e, true);
                         }
                     } else if (m.sw_cap) {
-                        ins = ins && !stop_probe(m, swt, sww, h, n, b0, b1, b2, rb, S.lmask, s, e, valid && !empty);
+                        ins = ins && !stop_probe_s(m, swtA, swwA, h, n, b0, b1, b2, rb, S.lmask, s, e, valid && !empty);
                     }
                     bool isnew = false;
                     if (csr_list) {  // append the bucket; the end of the dialogue orders and counts the list
