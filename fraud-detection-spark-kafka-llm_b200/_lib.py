@@ -27,6 +27,7 @@ SIGNATURES = {
     "fd_set_vocabulary": (C.c_int, [_p, _p, _p, _i32, _i32]),
     "fd_vocab_count": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _i32, _p, _i64, _p, _p]),
     "fd_hash_terms": (C.c_int, [_p, _p, _i32, _i32, _p]),
+    "fd_doc_freq": (C.c_int, [_p, _p, _p, _i64, _i32, _p, _p]),
     "fd_set_idf": (C.c_int, [_p, _p, _i32]),
     "fd_set_linear": (C.c_int, [_p, _p, _i32, _f64, _f64]),
     "fd_set_forest": (C.c_int, [_p, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _i32]),
@@ -38,6 +39,8 @@ SIGNATURES = {
     "fd_status": (C.c_int, [_p, _p]),
     "fd_transform_host": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _p]),
     "fd_transform_noalloc": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _p, _p, _p]),
+    "fd_eval_auc_roc": (C.c_int, [_p, _p, _i64, _p, _i64, _i32, _p, _p]),
+    "fd_eval_confusion2": (C.c_int, [_p, _p, _p, _i64, _p, _p]),
     "fd_workspace_bytes": (_i64, [_p, _i64]),
     "fd_reserve": (C.c_int, [_p, _i64]),
     "fd_launch_count": (_i64, [_p]),

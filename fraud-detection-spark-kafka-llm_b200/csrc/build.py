@@ -5,7 +5,7 @@ import sys
 from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SOURCES = ["fd_api.cu", "fd_api_compute.cu", "fd_rows.cu", "fd_main.cu", "fd_score.cu", "fd_train.cu", "fd_noalloc.cu"]
+SOURCES = ["fd_api.cu", "fd_api_compute.cu", "fd_rows.cu", "fd_main.cu", "fd_score.cu", "fd_train.cu", "fd_noalloc.cu", "fd_eval.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
               "-Xcompiler", "-fPIC"]
 LIB = os.path.join(HERE, "libfdb200.so")

@@ -478,11 +478,16 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
             uint32_t ta = tokA + 2u * (uint32_t)incl;
             uint32_t sp = SP;
             const uint32_t p1 = 32u * (uint32_t)lane + 1u;
-            while (sp) {
-                const int b = bfind_u32(sp);
+            while (sp) {  // two separators per trip
+                int b = bfind_u32(sp);
                 sts_u16(ta, p1 + (uint32_t)b);
-                ta -= 2u;
                 sp ^= 1u << b;
+                if (sp) {
+                    b = bfind_u32(sp);
+                    sts_u16(ta - 2u, p1 + (uint32_t)b);
+                    sp ^= 1u << b;
+                }
+                ta -= 4u;
             }
         }
         const int my_ll = L ? (32 * lane + 31 - __clz(L)) : -1;

@@ -31,6 +31,14 @@ __global__ void k_bin_csr(const int32_t* __restrict__ idx, const double* __restr
     }
 }
 
+// ---- IDF.fit, counting part: docFreq[j] = number of dialogues with a value > 0 at feature j ----------------
+// (a dialogue holds a feature at most once in CSR, so every stored entry with a positive value is one document)
+__global__ void k_doc_freq(const int32_t* __restrict__ idx, const double* __restrict__ val, long long nnz, unsigned long long* __restrict__ df) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride)
+        if (val[k] > 0.0) atomicAdd(df + idx[k], 1ULL);
+}
+
 // ---- bagging: Poisson(rate) bootstrap weights + weighted class totals of the root ------------------------
 // One thread draws 16 consecutive rows of one tree (one 16-byte store).  u = top 32 bits of splitmix64(key) with
 // key = seed, tree, row; the draw is the number of CDF thresholds <= u (thresholds precomputed on the host).
@@ -288,6 +296,22 @@ int fd_bin_csr(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int6
     long long g = (nnz + 255) / 256;
     if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
     k_bin_csr<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>(idx_dev, val_dev, nnz, thr_ptr_dev, thr_dev, out_bin_dev);
+    h->launches += 1;
+    FD_CUDA(h, cudaGetLastError());
+    return FD_OK;
+}
+
+int fd_doc_freq(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int64_t nnz, int32_t num_features, int64_t* out_doc_freq_dev,
+                void* stream) {
+    if (!h) return FD_ERR_INVALID;
+    if (nnz < 0 || num_features <= 0 || !out_doc_freq_dev || (nnz > 0 && (!idx_dev || !val_dev))) return set_err(h, FD_ERR_INVALID, "bad fd_doc_freq arguments");
+    FD_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    FD_CUDA(h, cudaMemsetAsync(out_doc_freq_dev, 0, (size_t)num_features * sizeof(int64_t), st));
+    if (nnz == 0) return FD_OK;
+    long long g = (nnz + 255) / 256;
+    if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
+    k_doc_freq<<<(unsigned)g, 256, 0, st>>>(idx_dev, val_dev, nnz, reinterpret_cast<unsigned long long*>(out_doc_freq_dev));
     h->launches += 1;
     FD_CUDA(h, cudaGetLastError());
     return FD_OK;

@@ -3,8 +3,10 @@
 (accuracy, weightedPrecision, weightedRecall, f1) and ``crosstab(labels, prediction)``.
 
 Spark semantics restated (mllib ``BinaryClassificationMetrics`` with numBins = 1000 on a single partition,
-``MulticlassMetrics``).  Implemented with torch tensor ops so the columns never leave the device; these are
-O(N log N) reductions over 8-byte columns, far off the hot path (no custom kernel needed)."""
+``MulticlassMetrics``).  Columns on a CUDA device go through the library's kernels (``fd_eval_auc_roc``: radix sort of the
+scores, group heads, cumulative positives, chunk points, trapezoid sum; ``fd_eval_confusion2``: the four counts of a binary
+problem), so they never leave the device; host columns, areaUnderPR and labels outside {0, 1} take the tensor-op
+restatement below, which is also what the kernels are tested against."""
 from __future__ import annotations
 
 from typing import Dict
@@ -23,6 +25,23 @@ def _col(data, name):
     return data[name] if not hasattr(data, "_cols") else data[name]
 
 
+_HANDLES = {}
+
+
+def _handle(device_index: int):
+    """One library handle per device for the evaluators (they need no model)."""
+    from . import _lib
+    if device_index not in _HANDLES:
+        _HANDLES[device_index] = _lib.Handle(device_index)
+    return _HANDLES[device_index]
+
+
+def _stream(t):
+    import ctypes as C
+    import torch
+    return C.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
 class BinaryClassificationEvaluator:
     """``pyspark.ml.evaluation.BinaryClassificationEvaluator`` (metricName areaUnderROC / areaUnderPR)."""
 
@@ -37,7 +56,18 @@ class BinaryClassificationEvaluator:
         raw = _t(_col(predictions, self.rawPredictionCol))
         score = raw[:, 1] if raw.ndim == 2 else raw
         y = _t(labels if labels is not None else _col(predictions, self.labelCol), like=score).to(score.device).to(torch.float64)
-        score = score.to(torch.float64)
+        if score.is_cuda and score.dtype == torch.float64 and self.metricName == "areaUnderROC":
+            from . import _lib
+            y = y.contiguous()
+            out = torch.zeros(3, dtype=torch.float64, device=score.device)
+            _handle(score.device.index).call("fd_eval_auc_roc", _lib.ptr(score), int(score.stride(0)) if score.numel() else 1, _lib.ptr(y),
+                                             int(score.numel()), int(self.numBins), _lib.ptr(out), _stream(score))
+            area, tp, tn = (float(v) for v in out.cpu().tolist())
+            x_last, y_last = (1.0 if tn > 0 else 0.0), (1.0 if tp > 0 else 0.0)
+            return area + (1.0 - x_last) * (1.0 + y_last) / 2.0  # the closing segment to (1, 1)
+        # scores compare as java.lang.Double does (by bit pattern: 0.0 > -0.0, two distinct scores): order-preserving int64 keys
+        bits = score.to(torch.float64).contiguous().view(torch.int64)
+        score = torch.where(bits < 0, ~bits ^ torch.iinfo(torch.int64).min, bits)
         order = torch.argsort(score, descending=True, stable=True)
         s, y = score[order], y[order]
         # counts per distinct score, in descending score order
@@ -76,6 +106,16 @@ def confusion_matrix(labels, prediction) -> Dict[str, np.ndarray]:
     import torch
     y = _t(labels)
     p = _t(prediction, like=y).to(y.device)
+    if y.is_cuda and y.numel():
+        from . import _lib
+        yd, pd = y.to(torch.float64).contiguous(), p.to(torch.float64).contiguous()
+        counts = torch.zeros(5, dtype=torch.int64, device=y.device)
+        _handle(y.device.index).call("fd_eval_confusion2", _lib.ptr(yd), _lib.ptr(pd), int(yd.numel()), _lib.ptr(counts), _stream(yd))
+        c = counts.cpu().numpy()
+        if c[4] == 0:  # binary labels and predictions: the kernel's four counts are the whole table
+            full = c[:4].reshape(2, 2)
+            seen = [v for v in (0, 1) if full[v, :].sum() + full[:, v].sum() > 0]
+            return {"labels": np.asarray(seen, dtype=np.float64), "matrix": full[np.ix_(seen, seen)].astype(np.int64)}
     vals = torch.unique(torch.cat([y.to(torch.float64), p.to(torch.float64)]))
     yi = torch.searchsorted(vals, y.to(torch.float64))
     pi = torch.searchsorted(vals, p.to(torch.float64))

@@ -409,8 +409,9 @@ class Pipeline:
         if idf:
             st = idf[0]
             if isinstance(st, S.IDF):
-                # docFreq[j] = documents with value > 0 at j (term counts are >= 1, so normally every stored entry counts)
-                df = torch.bincount(idx if bool((val > 0).all()) else idx[val > 0], minlength=nf)
+                # docFreq[j] = documents with value > 0 at j: counted by the library's kernel, summed over ranks below
+                df = torch.empty(nf, dtype=torch.int64, device=dev)
+                tf_model.handle(device).call("fd_doc_freq", _lib.ptr(idx), _lib.ptr(val), int(idx.numel()), int(nf), _lib.ptr(df), _stream_ptr(dev))
                 nd = torch.tensor([rowptr.numel() - 1], dtype=torch.int64, device=dev)
                 if dist.is_available() and dist.is_initialized():
                     dist.all_reduce(df)

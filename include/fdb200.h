@@ -95,6 +95,12 @@ int fd_vocab_count(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_de
 /* HashingTF.indexOf(term) for n terms on the HOST (no device work): out[i] = nonNegativeMod(
  * murmur3_x86_32(term_i bytes, seed 42), num_features).  terms = bytes back to back, offs int32[n+1]. */
 int fd_hash_terms(const uint8_t* terms, const int32_t* offs, int32_t n, int32_t num_features, int32_t* out);
+/* IDF.fit, counting part (fraud_detection_spark.py:53 via Pipeline.fit at :85-91; mllib IDF.DocumentFrequencyAggregator):
+ * out_doc_freq int64[num_features] (zeroed by the call) receives, per feature, the number of rows of the CSR matrix that
+ * hold it with a value > 0.  Ranks add their vectors (NCCL all-reduce by the caller) and the host applies
+ * idf = log((numDocs + 1) / (docFreq + 1)).  Asynchronous. */
+int fd_doc_freq(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int64_t nnz, int32_t num_features,
+                int64_t* out_doc_freq_dev, void* stream);
 /* IDFModel.idf (stages/3_IDF_58bd96296a82/data): dense f64[num_features]; NULL removes the stage. */
 int fd_set_idf(fd_handle* h, const double* idf, int32_t num_features);
 /* Binomial LogisticRegressionModel (stages/4_LogisticRegression_65ef69d6dfd9): dense coefficient
@@ -173,6 +179,19 @@ int fd_transform_noalloc(fd_handle* h, const uint8_t* text_dev, const int64_t* o
  * No counterpart in the reference: Spark sizes its executors' memory through spark.executor.memory. */
 int64_t fd_workspace_bytes(fd_handle* h, int64_t n_rows);
 int fd_reserve(fd_handle* h, int64_t n_rows);
+/* ---- evaluators on the transform output (fraud_detection_spark.py:101-119) -------------------------------- */
+/* BinaryClassificationEvaluator(metricName = "areaUnderROC"): mllib BinaryClassificationMetrics(scoreAndLabels, numBins) on
+ * one partition.  score_dev + i * score_stride (in doubles) is row i's score -- pass rawPrediction + 1 with stride 2 for the
+ * reference's column; label_dev f64[n] (> 0.5 = positive).  out_dev f64[3] receives {area over the points up to the last
+ * distinct score, positives, negatives}; the caller adds the closing segment to (1, 1), which is zero unless a class is
+ * absent.  Allocates and frees its scratch, synchronises `stream`. */
+int fd_eval_auc_roc(fd_handle* h, const double* score_dev, int64_t score_stride, const double* label_dev, int64_t n,
+                    int32_t num_bins, double* out_dev, void* stream);
+/* The counts behind MulticlassClassificationEvaluator (accuracy, weightedPrecision, weightedRecall, f1) and
+ * crosstab("labels", "prediction") for binary labels: out_counts int64[5] = rows with (label, prediction) = (0,0), (0,1),
+ * (1,0), (1,1), and rows holding any other value (the caller then falls back to a general tabulation).  Asynchronous. */
+int fd_eval_confusion2(fd_handle* h, const double* label_dev, const double* pred_dev, int64_t n, int64_t* out_counts_dev,
+                       void* stream);
 /* Number of kernel launches the handle has issued since creation (bench.py's gpu_launches). */
 int64_t fd_launch_count(fd_handle* h);
 

@@ -661,9 +661,17 @@ def area_under_roc(scores: Sequence[float], labels: Sequence[float], num_bins: i
     """``BinaryClassificationMetrics(scoreAndLabels, numBins).areaUnderROC`` on ONE partition: counts per distinct
     score (descending), optional down-sampling in chunks of ``distinct // numBins``, ROC points with (0,0) and
     (1,1) added, trapezoid rule summed left to right."""
+    # scores are keys of a JVM map and are sorted with java.lang.Double.compare: equality and order by bit pattern, so
+    # -0.0 and 0.0 are two distinct scores with 0.0 > -0.0
+    import struct
+
+    def jkey(v):
+        b = struct.unpack("<Q", struct.pack("<d", float(v)))[0]
+        return (b ^ 0xFFFFFFFFFFFFFFFF) if b >> 63 else (b | 0x8000000000000000)
+
     counts = {}
     for s, y in zip(scores, labels):
-        c = counts.setdefault(float(s), [0.0, 0.0])
+        c = counts.setdefault(jkey(s), [0.0, 0.0])
         c[0 if y > 0.5 else 1] += 1.0
     items = [(s, counts[s]) for s in sorted(counts, reverse=True)]
     grouping = len(items) // num_bins if num_bins > 0 else 0
