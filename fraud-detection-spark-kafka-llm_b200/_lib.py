@@ -42,9 +42,11 @@ SIGNATURES = {
     "fd_eval_auc_roc": (C.c_int, [_p, _p, _i64, _p, _i64, _i32, _p, _p]),
     "fd_eval_confusion2": (C.c_int, [_p, _p, _p, _i64, _p, _p]),
     "fd_workspace_bytes": (_i64, [_p, _i64]),
+    "fd_csc_scratch_bytes": (_i64, [_p, _i64, _i32]),
     "fd_reserve": (C.c_int, [_p, _i64]),
     "fd_launch_count": (_i64, [_p]),
     "fd_bin_csr": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p, _p]),
+    "fd_csc_build": (C.c_int, [_p, _p, _p, _p, _p, _i64, _i64, _i32, _p, _p, _p, _i64, _p]),
     "fd_rf_histogram": (C.c_int, [_p, _p, _p, _p, _p, _i64, _i32, _p, _p, _p, _i32, _p, _p, _i32, _p, _p]),
     "fd_rf_best_split": (C.c_int, [_p, _p, _i32, _p, _p, _p, _p, _p, _i32, _f64, _p, _p, _p, _p, _p, _p]),
     "fd_rf_bag_poisson": (C.c_int, [_p, C.c_uint64, _f64, _i32, _i64, _p, _p, _p, _p]),

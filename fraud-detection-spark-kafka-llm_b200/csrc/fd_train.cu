@@ -7,6 +7,8 @@
 // item, only that feature's COLUMN (CSC over this rank's row shard) and keeps the entries whose row
 // currently sits in the node.  Rows without the feature are accounted for after the cross-rank sum:
 // hist[bin_of_zero] += node_total - sum(explicit), which is exact because all counts are integers.
+#include <cub/cub.cuh>
+
 #include "fd_common.cuh"
 
 namespace fd {
@@ -28,6 +30,28 @@ __global__ void k_bin_csr(const int32_t* __restrict__ idx, const double* __restr
             else hi = mid;
         }
         out[k] = (uint8_t)(lo - base);
+    }
+}
+
+// ---- CSR -> CSC for the trainer: column entries (row | label << 31, bin), columns in feature order ------------
+// One warp per row packs its entries as (row | label << 31) << 8 | bin; a key-limited radix sort by feature id (CUB, only
+// the bits a feature id can have) brings every column together with its rows ascending; the sorted values are unpacked.
+__global__ void k_csc_pack(const int64_t* __restrict__ rowptr, const uint8_t* __restrict__ label, const uint8_t* __restrict__ bin,
+                           long long n_rows, unsigned long long* __restrict__ packed) {
+    const int lane = threadIdx.x & 31;
+    const long long nwarps = (long long)gridDim.x * (blockDim.x >> 5);
+    for (long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n_rows; r += nwarps) {
+        const long long a = rowptr[r], b = rowptr[r + 1];
+        const unsigned long long head = ((unsigned long long)(uint32_t)r | ((unsigned long long)(label[r] ? 1u : 0u) << 31)) << 8;
+        for (long long k = a + lane; k < b; k += 32) packed[k] = head | (unsigned long long)bin[k];
+    }
+}
+__global__ void k_csc_unpack(const unsigned long long* __restrict__ packed, long long nnz, uint32_t* __restrict__ rowidx, uint8_t* __restrict__ bin) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) {
+        const unsigned long long v = packed[k];
+        rowidx[k] = (uint32_t)(v >> 8);
+        bin[k] = (uint8_t)v;
     }
 }
 
@@ -297,6 +321,62 @@ int fd_bin_csr(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int6
     if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
     k_bin_csr<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>(idx_dev, val_dev, nnz, thr_ptr_dev, thr_dev, out_bin_dev);
     h->launches += 1;
+    FD_CUDA(h, cudaGetLastError());
+    return FD_OK;
+}
+
+// bits of a feature id; bytes of scratch fd_csc_build needs: sorted keys + packed values in and out + the sort's workspace
+static int csc_end_bit(int32_t num_features) {
+    int end_bit = 1;
+    while (end_bit < 31 && (1LL << end_bit) < (long long)num_features) ++end_bit;
+    return end_bit;
+}
+static size_t csc_scratch_need(int64_t nnz, int end_bit, size_t* tmp_bytes) {
+    size_t tb = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, (const int32_t*)nullptr, (int32_t*)nullptr, (const unsigned long long*)nullptr,
+                                    (unsigned long long*)nullptr, (int)nnz, 0, end_bit, (cudaStream_t)0);
+    if (tmp_bytes) *tmp_bytes = tb;
+    const size_t N = (size_t)nnz;
+    return ((N * 4 + 255) & ~(size_t)255) + 2 * N * 8 + 256 + tb;
+}
+
+int64_t fd_csc_scratch_bytes(fd_handle* h, int64_t nnz, int32_t num_features) {
+    if (!h) return FD_ERR_INVALID;
+    if (nnz < 0 || nnz >= (1LL << 31) || num_features <= 0) return set_err(h, FD_ERR_INVALID, "bad fd_csc_scratch_bytes arguments");
+    return (int64_t)csc_scratch_need(nnz, csc_end_bit(num_features), nullptr);
+}
+
+int fd_csc_build(fd_handle* h, const int64_t* rowptr_dev, const int32_t* idx_dev, const uint8_t* bin_dev, const uint8_t* label_dev,
+                 int64_t n_rows, int64_t nnz, int32_t num_features, uint32_t* out_rowidx_dev, uint8_t* out_bin_dev, void* scratch_dev,
+                 int64_t scratch_bytes, void* stream) {
+    if (!h) return FD_ERR_INVALID;
+    if (n_rows < 0 || nnz < 0 || num_features <= 0 || (nnz > 0 && (!rowptr_dev || !idx_dev || !bin_dev || !label_dev || !out_rowidx_dev || !out_bin_dev)))
+        return set_err(h, FD_ERR_INVALID, "bad fd_csc_build arguments");
+    if (n_rows >= (1LL << 31) || nnz >= (1LL << 31)) return set_err(h, FD_ERR_LIMIT, "fd_csc_build: at most 2^31 - 1 rows and entries per rank");
+    if (nnz == 0) return FD_OK;
+    FD_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int end_bit = csc_end_bit(num_features);
+    const size_t N = (size_t)nnz;
+    size_t tmp_bytes = 0;
+    const size_t need = csc_scratch_need(nnz, end_bit, &tmp_bytes);
+    if (!scratch_dev || (size_t)scratch_bytes < need)
+        return set_err(h, FD_ERR_CAPACITY, "fd_csc_build needs %zu bytes of scratch (fd_csc_scratch_bytes), got %lld", need,
+                       (long long)scratch_bytes);
+    char* buf = static_cast<char*>(scratch_dev);
+    int32_t* keys_out = reinterpret_cast<int32_t*>(buf);
+    unsigned long long* vin = reinterpret_cast<unsigned long long*>(buf + ((N * 4 + 255) & ~(size_t)255));
+    unsigned long long* vout = vin + N;
+    void* tmp = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(vout + N) + 255) & ~(uintptr_t)255);
+    long long g = (n_rows + 7) / 8;
+    if (g > (long long)h->sm_count * 16) g = (long long)h->sm_count * 16;
+    if (g < 1) g = 1;
+    k_csc_pack<<<(unsigned)g, 256, 0, st>>>(rowptr_dev, label_dev, bin_dev, n_rows, vin);
+    FD_CUDA(h, cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, idx_dev, keys_out, vin, vout, (int)nnz, 0, end_bit, st));
+    long long g2 = (nnz + 255) / 256;
+    if (g2 > (long long)h->sm_count * 32) g2 = (long long)h->sm_count * 32;
+    k_csc_unpack<<<(unsigned)g2, 256, 0, st>>>(vout, nnz, out_rowidx_dev, out_bin_dev);
+    h->launches += 2;
     FD_CUDA(h, cudaGetLastError());
     return FD_OK;
 }

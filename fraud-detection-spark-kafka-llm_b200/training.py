@@ -375,6 +375,23 @@ class CudaTreeBackend:
         self.h.call("fd_bin_csr", _lib.ptr(idx), _lib.ptr(val), idx.numel(), _lib.ptr(thr_ptr), _lib.ptr(thr), _lib.ptr(out), self._st())
         return out
 
+    def _csc_scratch(self, nnz, n_features) -> int:
+        need = int(self.h.lib.fd_csc_scratch_bytes(self.h.h, nnz, n_features))
+        if need < 0:
+            self.h.check(need)
+        return need
+
+    def csc_build(self, rowptr, idx, bins, labels, n_features: int):
+        """-> (rowidx i32 [nnz] = row | label << 31, bin u8 [nnz]) ordered by (feature, row): fd_csc_build."""
+        t = self.torch
+        nnz = idx.numel()
+        rowidx = t.empty(nnz, dtype=t.int32, device=self.device)
+        out_bin = t.empty(nnz, dtype=t.uint8, device=self.device)
+        scratch = t.empty(self._csc_scratch(nnz, int(n_features)), dtype=t.uint8, device=self.device)  # (from torch's caching allocator)
+        self.h.call("fd_csc_build", _lib.ptr(rowptr), _lib.ptr(idx), _lib.ptr(bins), _lib.ptr(labels), rowptr.numel() - 1, nnz, int(n_features),
+                    _lib.ptr(rowidx), _lib.ptr(out_bin), _lib.ptr(scratch), scratch.numel(), self._st())
+        return rowidx, out_bin
+
     def bag_poisson(self, seed: int, rate: float, n_trees: int, label):
         """-> (bagw u8 [n_trees, n_rows], root i64 [n_trees, 2]): Poisson(rate) bootstrap weights and the weighted class
         counts of this rank's rows, one kernel (fd_rf_bag_poisson)."""
@@ -524,19 +541,24 @@ class ForestTrainer:
         d_nsplits = torch.from_numpy(n_splits).to(dev)
         d_bz = torch.from_numpy(bin_of_zero).to(dev)
         bins = self.b.bin_csr(idx, val, d_thr_ptr, d_thr)
-        counts = rowptr[1:] - rowptr[:-1]
-        row_of = torch.repeat_interleave(torch.arange(n_local, dtype=torch.int32, device=dev), counts)
-        order = torch.argsort(idx, stable=True)
         labels = labels.to(dev).to(torch.uint8).contiguous()
         if self.max_depth > 22:
             raise ValueError("maxDepth > 22 is not supported (node ids share a 32-bit word with the bag weight)")
         # column entries carry (row | label << 31): the histogram kernel then needs a single gather per entry
-        row_lab = row_of | torch.repeat_interleave(labels.to(torch.int32) << 31, counts)
-        csc = (torch.zeros(self.F + 1, dtype=torch.int64, device=dev), row_lab[order].contiguous(), bins[order].contiguous())
-        del row_lab
-        torch.cumsum(torch.bincount(idx, minlength=self.F), 0, out=csc[0][1:])
-        col_len = np.diff(csc[0].cpu().numpy())
-        del order, row_of, bins
+        colptr = torch.zeros(self.F + 1, dtype=torch.int64, device=dev)
+        torch.cumsum(torch.bincount(idx, minlength=self.F), 0, out=colptr[1:])
+        if hasattr(self.b, "csc_build"):
+            rowidx, cbins = self.b.csc_build(rowptr, idx, bins, labels, self.F)
+        else:  # stand-in backends of the CPU orchestration tests
+            counts = rowptr[1:] - rowptr[:-1]
+            row_of = torch.repeat_interleave(torch.arange(n_local, dtype=torch.int32, device=dev), counts)
+            order = torch.argsort(idx, stable=True)
+            row_lab = row_of | torch.repeat_interleave(labels.to(torch.int32) << 31, counts)
+            rowidx, cbins = row_lab[order].contiguous(), bins[order].contiguous()
+            del order, row_of, row_lab
+        csc = (colptr, rowidx, cbins)
+        col_len = np.diff(colptr.cpu().numpy())
+        del bins
         tt = self._tick("bin+csc", tt)
         # ---- bagging
         root = None

@@ -201,6 +201,15 @@ int64_t fd_launch_count(fd_handle* h);
  * thr_ptr int32[num_features+1] indexes thr f64[]. */
 int fd_bin_csr(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int64_t nnz,
                const int32_t* thr_ptr_dev, const double* thr_dev, uint8_t* out_bin_dev, void* stream);
+/* The trainer's column view of this rank's binned rows (Spark keeps TreePoint rows; here a histogram pass walks COLUMNS):
+ * out_rowidx u32[nnz] = row index with the row's label in bit 31, out_bin u8[nnz], both ordered by (feature, row) -- the
+ * stable order of the CSR entries sorted by idx.  The column pointers are the prefix sums of the features' entry counts
+ * (caller).  Radix sort over the bits of a feature id only.  scratch_dev: caller-owned device memory of at least
+ * fd_csc_scratch_bytes(h, nnz, num_features) bytes -- about 32 per entry -- (FD_ERR_CAPACITY otherwise).  Asynchronous. */
+int64_t fd_csc_scratch_bytes(fd_handle* h, int64_t nnz, int32_t num_features);
+int fd_csc_build(fd_handle* h, const int64_t* rowptr_dev, const int32_t* idx_dev, const uint8_t* bin_dev, const uint8_t* label_dev,
+                 int64_t n_rows, int64_t nnz, int32_t num_features, uint32_t* out_rowidx_dev, uint8_t* out_bin_dev, void* scratch_dev,
+                 int64_t scratch_bytes, void* stream);
 /* BaggedPoint.convertToBaggedRDD (bootstrap = true, reached from RandomForestClassifier, fraud_detection_spark.py:67-74):
  * out_bagw u8[n_trees, n_rows] = Poisson(rate) draws (clamped to 255) from a counter-based generator keyed by
  * (seed, tree, row) -- reproducible, independent of the launch shape; not Spark's XORShift stream (bag weights are an
