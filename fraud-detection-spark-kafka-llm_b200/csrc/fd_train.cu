@@ -126,23 +126,50 @@ __global__ void __launch_bounds__(256) k_rf_bag_poisson(uint64_t seed, BagCdf cd
     }
 }
 
+// ---- cache policy of the column walks ---------------------------------------------------------------------
+// A histogram / advance pass streams column entries (read once) and gathers state[tree, row] at scattered rows.  The
+// warps in flight work on one or two trees at a time, whose state rows (4 B x rows) fit the L2 -- unless the stream
+// pushes them out, and then every gather is a 32-byte DRAM sector (measured: 38 B of DRAM per visited entry).  So the
+// stream is loaded evict-first and the state words with an evict-last L2 policy.
+__device__ __forceinline__ uint64_t l2_keep_policy() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint32_t ld_keep_u32(const uint32_t* p, uint64_t policy) {
+    uint32_t v;
+    asm volatile("ld.global.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(policy) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_keep_u32(uint32_t* p, uint32_t v, uint64_t policy) {
+    asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(policy) : "memory");
+}
+
 // ---- binSeqOp: one warp per (item, column segment) ---------------------------------------------------
 // item = (tree, node, feature).  The warp walks its segment of the feature's column, keeps entries whose
 // row is in the node, and adds the row's bag weight to a warp-private shared-memory histogram
 // [32 bins][2 classes]; the non-zero cells are then added to the item's global histogram.
 // Per entry ONE gather: the row's label rides in bit 31 of the column's row index, and the row's node id and
 // bag weight share one word, state[tree, row] = node_id << 8 | bag_weight.
-__global__ void __launch_bounds__(256) k_rf_histogram(const int64_t* __restrict__ colptr, const uint32_t* __restrict__ rowidx,
+constexpr int WALK_WARPS = 2;  // warps per CTA of the column walks (see the scheduling note below)
+
+// Scheduling: ONE unit per warp and a grid as long as the unit list, not a persistent grid-stride loop.  Units are in
+// (tree, node, feature) order and differ in length by three orders of magnitude; under a grid-stride loop the warps
+// with short units run far ahead, the units in flight spread over dozens of trees and every state gather becomes a DRAM
+// sector (measured: 332 GB read by one launch).  The hardware hands CTAs out in index order, so with small CTAs the
+// units in flight are always the next ~9,500 of the list -- one or two trees, whose state rows stay in the L2.
+__global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_histogram(const int64_t* __restrict__ colptr, const uint32_t* __restrict__ rowidx,
                                                       const uint8_t* __restrict__ bin, const uint32_t* __restrict__ state,
                                                       long long n_rows, int n_units, const int32_t* __restrict__ unit_item,
                                                       const int32_t* __restrict__ unit_seg, int seg_len,
                                                       const int32_t* __restrict__ item_tree, const int32_t* __restrict__ item_node,
                                                       const int32_t* __restrict__ item_feat, unsigned int* __restrict__ hist) {
-    __shared__ unsigned int sh[8][HB * 2];
+    __shared__ unsigned int sh[WALK_WARPS][HB * 2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned int* h = sh[warp];
-    const int nwarps = gridDim.x * 8;
-    for (int u = blockIdx.x * 8 + warp; u < n_units; u += nwarps) {
+    const uint64_t keep = l2_keep_policy();
+    const int u = blockIdx.x * WALK_WARPS + warp;
+    if (u < n_units) {
         h[lane] = 0u;
         h[32 + lane] = 0u;
         __syncwarp();
@@ -153,17 +180,16 @@ __global__ void __launch_bounds__(256) k_rf_histogram(const int64_t* __restrict_
         const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
         const uint32_t* st = state + (long long)t * n_rows;
         for (long long e = c0 + lane; e < c1; e += 32) {
-            const uint32_t rl = rowidx[e];
-            const uint32_t s = st[rl & 0x7FFFFFFFu];
+            const uint32_t rl = __ldcs(rowidx + e);
+            const uint32_t s = ld_keep_u32(st + (rl & 0x7FFFFFFFu), keep);
             const uint32_t w = s & 255u;
-            if ((s >> 8) == node && w) atomicAdd(&h[(int)bin[e] * 2 + (int)(rl >> 31)], w);
+            if ((s >> 8) == node && w) atomicAdd(&h[(int)__ldcs(bin + e) * 2 + (int)(rl >> 31)], w);
         }
         __syncwarp();
         unsigned int* g = hist + (size_t)item * (HB * 2);
         const unsigned int a = h[lane], b = h[32 + lane];
         if (a) atomicAdd(g + lane, a);
         if (b) atomicAdd(g + 32 + lane, b);
-        __syncwarp();
     }
 }
 
@@ -266,15 +292,16 @@ __global__ void __launch_bounds__(128) k_rf_best_split(const unsigned int* __res
 
 // ---- move rows to their children ------------------------------------------------------------------------
 // explicit entries of the split feature: one warp per (split node, column segment)
-__global__ void __launch_bounds__(256) k_rf_advance_explicit(const int64_t* __restrict__ colptr, const uint32_t* __restrict__ rowidx,
+__global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_advance_explicit(const int64_t* __restrict__ colptr, const uint32_t* __restrict__ rowidx,
                                                              const uint8_t* __restrict__ bin, uint32_t* __restrict__ state,
                                                              long long n_rows, int n_units, const int32_t* __restrict__ unit_item,
                                                              const int32_t* __restrict__ unit_seg, int seg_len,
                                                              const int32_t* __restrict__ split_tree, const int32_t* __restrict__ split_node,
                                                              const int32_t* __restrict__ split_feat, const int32_t* __restrict__ split_bin) {
     const int lane = threadIdx.x & 31;
-    const int nwarps = gridDim.x * 8;
-    for (int u = blockIdx.x * 8 + (threadIdx.x >> 5); u < n_units; u += nwarps) {
+    const uint64_t keep = l2_keep_policy();
+    const int u = blockIdx.x * WALK_WARPS + (threadIdx.x >> 5);
+    if (u < n_units) {
         const int s = unit_item[u];
         const uint32_t node = (uint32_t)split_node[s];
         const int f = split_feat[s], sb = split_bin[s];
@@ -282,9 +309,9 @@ __global__ void __launch_bounds__(256) k_rf_advance_explicit(const int64_t* __re
         const long long c0 = colptr[f] + (long long)unit_seg[u] * seg_len;
         const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
         for (long long e = c0 + lane; e < c1; e += 32) {
-            const uint32_t r = rowidx[e] & 0x7FFFFFFFu;
-            const uint32_t v = st[r];
-            if ((v >> 8) == node) st[r] = ((((int)bin[e] <= sb) ? 2u * node : 2u * node + 1u) << 8) | (v & 255u);
+            const uint32_t r = __ldcs(rowidx + e) & 0x7FFFFFFFu;
+            const uint32_t v = ld_keep_u32(st + r, keep);
+            if ((v >> 8) == node) st_keep_u32(st + r, ((((int)__ldcs(bin + e) <= sb) ? 2u * node : 2u * node + 1u) << 8) | (v & 255u), keep);
         }
     }
 }
@@ -407,9 +434,8 @@ int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const uint32_t* row
     cudaStream_t st = (cudaStream_t)stream;
     FD_CUDA(h, cudaMemsetAsync(out_hist_dev, 0, (size_t)n_items * HB * 2 * sizeof(uint32_t), st));
     if (n_units == 0) return FD_OK;
-    int g = (n_units + 7) / 8;
-    if (g > h->sm_count * 8) g = h->sm_count * 8;
-    k_rf_histogram<<<g, 256, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, state_dev, n_rows, n_units, unit_item_dev,
+    const int g = (n_units + WALK_WARPS - 1) / WALK_WARPS;
+    k_rf_histogram<<<g, WALK_WARPS * 32, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, state_dev, n_rows, n_units, unit_item_dev,
                                       unit_seg_dev, seg_len, item_tree_dev, item_node_dev, item_feat_dev, out_hist_dev);
     h->launches += 1;
     FD_CUDA(h, cudaGetLastError());
@@ -474,9 +500,8 @@ int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowid
     FD_CUDA(h, cudaSetDevice(h->device));
     cudaStream_t st = (cudaStream_t)stream;
     if (n_units > 0) {
-        int g = (n_units + 7) / 8;
-        if (g > h->sm_count * 8) g = h->sm_count * 8;
-        k_rf_advance_explicit<<<g, 256, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, state_dev, n_rows, n_units, unit_item_dev, unit_seg_dev,
+        const int g = (n_units + WALK_WARPS - 1) / WALK_WARPS;
+        k_rf_advance_explicit<<<g, WALK_WARPS * 32, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, state_dev, n_rows, n_units, unit_item_dev, unit_seg_dev,
                                                  seg_len, split_tree_dev, split_node_dev, split_feat_dev, split_bin_dev);
         h->launches += 1;
     }

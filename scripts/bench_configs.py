@@ -205,8 +205,10 @@ def run_c4(ctx):
     return res
 
 
-def _c5_fit(ctx, n_local, trees, depth, profile, seed_base=500):
-    """One Pipeline.fit of the RandomForest on this rank's n_local synthetic rows -> (seconds max over ranks, model, stats)."""
+def _c5_fit(ctx, n_local, trees, depth, profile, seed_base=500, release=True):
+    """One Pipeline.fit of the RandomForest on this rank's n_local synthetic rows -> (seconds max over ranks, model, stats).
+    ``release``: hand the caching allocator's blocks back to the driver afterwards, so that the next fit starts from an
+    empty pool and pays every cudaMalloc again."""
     dev = ctx.dev
     planted = {"ids": list(range(ctx.corpus.n_stop + 300, ctx.corpus.n_stop + 320)), "rate": 0.05}
     pk, lab = ctx.corpus.sample(n_local, tokens=200, device=dev, seed=seed_base + ctx.rank, planted=planted)
@@ -227,7 +229,8 @@ def _c5_fit(ctx, n_local, trees, depth, profile, seed_base=500):
     secs = ctx.maxreduce(time.perf_counter() - t0)
     tr.PROFILE_DEFAULT = False
     del pk, lab
-    torch.cuda.empty_cache()
+    if release:
+        torch.cuda.empty_cache()
     return secs, model, planted
 
 
@@ -241,8 +244,10 @@ def run_c5(ctx, rows=10_000_000, trees=100, depth=10, weak=True):
     modes = [("strong", rows // ctx.world)] + ([("weak", rows)] if weak and ctx.world > 1 else [])
     _c5_fit(ctx, 50_000, 4, 3, profile=False)  # warm-up: kernels loaded, collectives set up (steady state is what is timed)
     for name, n_local in modes:
-        secs, model, planted = _c5_fit(ctx, n_local, trees, depth, profile=False)
+        secs, model, planted = _c5_fit(ctx, n_local, trees, depth, profile=False, release=False)
         rf = model.stages[-1]
+        warm_secs, wmodel, _ = _c5_fit(ctx, n_local, trees, depth, profile=False, release=False)  # same fit, allocator pool kept
+        del wmodel
         test, tlab = ctx.corpus.sample(20000, tokens=200, device=ctx.dev, seed=999, planted=planted)
         auc = roc_auc_score(tlab.cpu().numpy(), model.transform(test)["rawPrediction"][:, 1].cpu().numpy())
         stats = dict(getattr(rf, "trainer_stats", {}))
@@ -251,10 +256,19 @@ def run_c5(ctx, rows=10_000_000, trees=100, depth=10, weak=True):
         pstats = getattr(pmodel.stages[-1], "trainer_stats", {})
         phases = dict(pstats.get("phases_s", {}))
         phases.update({"pipeline:" + k: v for k, v in pstats.get("pipeline_phases_s", {}).items()})
+        if ctx.world > 1:  # the same phases on every rank (a phase that waits for a collective shows the slowest rank's time)
+            keys = sorted(phases)
+            mine = torch.tensor([phases[k] for k in keys], dtype=torch.float64, device=ctx.dev)
+            allp = [torch.zeros_like(mine) for _ in range(ctx.world)]
+            ctx.dist.all_gather(allp, mine)
+            spread = {k: [round(float(allp[r][i]), 4) for r in range(ctx.world)] for i, k in enumerate(keys)}
+        else:
+            spread = None
         out[name] = {"rows_total": n_local * ctx.world, "rows_per_gpu": n_local, "fit_seconds": secs, "rows_per_s": n_local * ctx.world / secs,
                      "trees_per_s": trees / secs, "nodes": sum(t.n_nodes for t in rf.trees), "test_auc": float(auc),
                      "allreduce_calls": stats.get("allreduce_calls"), "hist_bytes": stats.get("hist_bytes"),
-                     "phases_s": {k: round(v, 4) for k, v in phases.items()}, "fit_seconds_with_phase_timers": psecs}
+                     "phases_s": {k: round(v, 4) for k, v in phases.items()}, "fit_seconds_with_phase_timers": psecs,
+                     "fit_seconds_warm_pool": warm_secs, "phases_s_by_rank": spread}
         del model, pmodel
     if ctx.world == 1:
         out["weak"] = out["strong"]
