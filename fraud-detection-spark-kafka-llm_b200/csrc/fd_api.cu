@@ -288,7 +288,12 @@ int fd_create(int device, fd_handle** out) {
         return FD_ERR_CUDA;
     }
     cudaDeviceProp prop;
-    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) h->sm_count = prop.multiProcessorCount;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) {
+        h->sm_count = prop.multiProcessorCount;
+        if (!prop.canMapHostMemory || !prop.unifiedAddressing) h->direct_host = 0;
+    }
+    const char* e = getenv("FDB200_DIRECT_HOST");
+    if (e && e[0] == '0') h->direct_host = 0;
     *out = h;
     return FD_OK;
 }

@@ -304,6 +304,64 @@ int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* off
         if (!h->hs[i]) FD_CUDA(h, cudaStreamCreateWithFlags(&h->hs[i], cudaStreamNonBlocking));
     if (!h->pinned_ctrl) FD_CUDA(h, cudaMallocHost((void**)&h->pinned_ctrl, 4 * sizeof(Ctrl)));
 
+    // ---- micro-batches whose buffers are pinned (mapped) host memory: no copies at all.  The kernels read the dialogues
+    // and offsets from host memory through the same TMA windows and write the three columns straight back, so the transfer
+    // overlaps the work window by window and the call is two launches, the status read and one synchronise -- instead
+    // of two H2D and three D2H copies around them.  (A 16-byte block never straddles a page, so the kernels' reads up to the
+    // next multiple of 16 stay inside the pinned pages.)  Larger batches keep the chunked three-stream copy pipeline below.
+    constexpr int64_t DIRECT_MAX_BYTES = 8 << 20;
+    if (n_rows <= (1 << 16) && offs_host[n_rows] - offs_host[0] <= DIRECT_MAX_BYTES && h->direct_host) {
+        const void* dp[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+        const void* hp[5] = {text_host, offs_host, out_pred_host, out_prob_host, out_raw_host};
+        bool ok = ((uintptr_t)text_host & 15) == 0;
+        for (int i = 0; i < 5 && ok; ++i) {
+            cudaPointerAttributes at;
+            if (cudaPointerGetAttributes(&at, hp[i]) != cudaSuccess) {
+                cudaGetLastError();
+                ok = false;
+            } else {
+                ok = at.type == cudaMemoryTypeHost && at.devicePointer != nullptr;
+                dp[i] = at.devicePointer;
+            }
+        }
+        if (ok && ((uintptr_t)dp[0] & 15) == 0) {
+            const size_t need = slot_bytes(n_rows);
+            if (need > h->hbuf_bytes[0]) {
+                if (h->hbuf[0]) {
+                    FD_CUDA(h, cudaStreamSynchronize(h->hs[0]));
+                    FD_CUDA(h, cudaFree(h->hbuf[0]));
+                    h->hbuf[0] = nullptr;
+                }
+                FD_CUDA(h, cudaMalloc((void**)&h->hbuf[0], need));
+                h->hbuf_bytes[0] = need;
+                FD_CUDA(h, cudaMemsetAsync(h->hbuf[0], 0, 256, h->hs[0]));
+            }
+            cudaStream_t st = h->hs[0];
+            RowArgs a;
+            memset(&a, 0, sizeof(a));
+            fill_slot(a, h->hbuf[0], n_rows);
+            a.text = static_cast<const uint8_t*>(dp[0]);
+            a.offs = static_cast<const int64_t*>(dp[1]);
+            a.n_rows = n_rows;
+            a.flags = flags;
+            a.host_bytes = offs_host[n_rows] - offs_host[0];
+            a.m = h->m;  // (after prepare_fused)
+            a.pred = static_cast<double*>(const_cast<void*>(dp[2]));
+            a.prob = static_cast<double*>(const_cast<void*>(dp[3]));
+            a.raw = static_cast<double*>(const_cast<void*>(dp[4]));
+            FD_CUDA(h, cudaMemsetAsync(a.ctrl, 0, CTRL_CLEAR_BYTES, st));
+            FD_CUDA(h, launch_rows(h, mode, a, st));
+            FD_CUDA(h, cudaMemcpyAsync(h->pinned_ctrl + 1, h->hbuf[0], sizeof(Ctrl), cudaMemcpyDeviceToHost, st));
+            FD_CUDA(h, cudaStreamSynchronize(st));
+            if (h->pinned_ctrl[1].status != FD_OK) {
+                const int status = h->pinned_ctrl[1].status;
+                cudaMemsetAsync(&reinterpret_cast<Ctrl*>(h->hbuf[0])->status, 0, sizeof(int), st);
+                return set_err(h, status, "a dialogue exceeds the supported number of distinct hashed terms (%d)", (1 << BIG_LOG2) * 3 / 4);
+            }
+            return FD_OK;
+        }
+    }
+
     constexpr int64_t CHUNK_BYTES = 64 << 20;  // pinned copies reach their full rate (55.5 GB/s here) from about 64 MiB; 24 MiB chunks ran at ~50
     constexpr int64_t CHUNK_ROWS = 1 << 18;
     int64_t r0 = 0;

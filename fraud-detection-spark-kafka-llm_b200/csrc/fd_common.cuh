@@ -142,6 +142,7 @@ struct fd_handle {
     char* hbuf[3] = {nullptr, nullptr, nullptr};
     size_t hbuf_bytes[3] = {0, 0, 0};
     fd::Ctrl* pinned_ctrl = nullptr;
+    int direct_host = 1;  // fd_transform_host may read / write pinned caller buffers in place (FDB200_DIRECT_HOST=0 turns it off)
     // host copies needed to (re)build nodes_s when the idf vector or the forest changes
     std::vector<fd::Node> host_nodes;
     std::vector<double> host_idf;

@@ -306,9 +306,14 @@ class PipelineModel:
         if output == "host" and not pk.is_device:
             data = pk.data if isinstance(pk.data, np.ndarray) else pk.data.numpy()
             offs = pk.offs if isinstance(pk.offs, np.ndarray) else pk.offs.numpy()
-            pred = np.empty(n, dtype=np.float64)
-            prob = np.empty((n, 2), dtype=np.float64)
-            raw = np.empty((n, 2), dtype=np.float64)
+            if torch.is_tensor(pk.data) and pk.data.is_pinned() and torch.is_tensor(pk.offs) and pk.offs.is_pinned():
+                # pinned input: pinned outputs too (from torch's caching host allocator), so that a micro-batch is read
+                # and written in place by the kernels
+                pred, prob, raw = (torch.empty(s_, dtype=torch.float64, pin_memory=True).numpy() for s_ in ((n,), (n, 2), (n, 2)))
+            else:
+                pred = np.empty(n, dtype=np.float64)
+                prob = np.empty((n, 2), dtype=np.float64)
+                raw = np.empty((n, 2), dtype=np.float64)
             h.call("fd_transform_host", _lib.ptr(data), _lib.ptr(offs), n, flags, _lib.ptr(pred), _lib.ptr(prob), _lib.ptr(raw))
             return TransformResult(dict(zip(names, (pred, prob, raw))), n)
         dev = torch.device("cuda", h.device)

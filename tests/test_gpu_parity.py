@@ -356,6 +356,41 @@ def test_host_buffer_transform_matches_device(fd):
     assert model.handle().launch_count() > 0
 
 
+def test_pinned_host_buffers_are_read_in_place(fd, shipped_model_dir):
+    """A micro-batch whose buffers are pinned host memory is read and written by the kernels in place (no staging copies):
+    same columns as the copying path (pageable buffers) and as the oracle -- long rows, deferred rows, empty rows, a text
+    buffer that ends exactly at its last (unaligned) byte, and a batch that starts in the middle of the buffer."""
+    import torch
+    from helpers import messy_texts
+    model = fd.PipelineModel.load(shipped_model_dir)
+    ora = oracle_for(model)
+    rows = _long_rows() + ["", " ", "a"] + messy_texts(60, seed=9) + ["", "trailing token"]
+    pk = fd.PackedText.from_strings(rows)
+    n = pk.n_rows
+    total = int(pk.offs[-1])
+    assert total % 16 != 0
+    exp = ora.transform([t.encode() for t in rows])
+    h = model.handle()
+    P = importlib.import_module("fraud-detection-spark-kafka-llm_b200._lib").ptr
+    data = torch.from_numpy(np.ascontiguousarray(pk.data[:total])).pin_memory()   # ends at the last byte of the text
+    offs = torch.from_numpy(pk.offs.copy()).pin_memory()
+    outs = [torch.full(s_, float("nan"), dtype=torch.float64).pin_memory() for s_ in ((n,), (n, 2), (n, 2))]
+    h.call("fd_transform_host", P(data), P(offs), n, 1, P(outs[0]), P(outs[1]), P(outs[2]))
+    got = dict(zip(("prediction", "probability", "rawPrediction"), (o.numpy() for o in outs)))
+    _check_scores(got, exp)
+    # pageable buffers: the copying path
+    pouts = [np.full(s_, np.nan) for s_ in ((n,), (n, 2), (n, 2))]
+    h.call("fd_transform_host", P(pk.data), P(pk.offs), n, 1, P(pouts[0]), P(pouts[1]), P(pouts[2]))
+    for a_, b_ in zip(outs, pouts):
+        assert np.array_equal(a_.numpy(), b_)
+    # rows [k, n) of the same buffers: offsets that do not start at zero, outputs written from their first element
+    k = 7
+    sub = [torch.full(s_, float("nan"), dtype=torch.float64).pin_memory() for s_ in ((n - k,), (n - k, 2), (n - k, 2))]
+    h.call("fd_transform_host", P(data), P(offs[k:]), n - k, 1, P(sub[0]), P(sub[1]), P(sub[2]))
+    for a_, b_ in zip(outs, sub):
+        assert np.array_equal(a_.numpy()[k:], b_.numpy())
+
+
 def test_sharded_transform_equals_whole(fd, shipped_model_dir):
     """Byte-balanced shards (one per rank in a multi-GPU job; no collective) give the same rows as one call."""
     model = fd.PipelineModel.load(shipped_model_dir)
