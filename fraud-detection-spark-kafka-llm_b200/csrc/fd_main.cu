@@ -75,18 +75,25 @@ __device__ __forceinline__ void classify4(uint32_t x, uint32_t& l, uint32_t& s, 
     }
 }
 
+// long_stop_word_equal with the window given by 32-bit shared addresses: the callers' hot loops then never hold (or rebuild,
+// at twenty instructions a time) the generic pointers that only this rare comparison needs
+static __device__ __noinline__ bool long_stop_word_equal_s(const uint8_t* word, uint32_t rbA, uint32_t lmA, int s, int e) {
+    return long_stop_word_equal(word, reinterpret_cast<const uint8_t*>(__cvta_shared_to_generic(rbA)),
+                                reinterpret_cast<const uint32_t*>(__cvta_shared_to_generic(lmA)), s, e);
+}
+
 // is the in-window token a stop word?  h = murmur3 of its kept bytes, n = their number, b0..b2 = the first 12 of them;
 // [s, e) locates it in the window (for the byte compare of words longer than 12 bytes).  cand: the lane holds a non-empty
 // token at all.  Straight-line: the word record is loaded unconditionally, only long words call out.
 __device__ __forceinline__ bool stop_probe(const Model& m, const uint32_t* swt, const uint4* sww, uint32_t h, uint32_t n, uint32_t b0,
-                                           uint32_t b1, uint32_t b2, const uint8_t* rb, const uint32_t* lmask, int s, int e, bool cand) {
+                                           uint32_t b1, uint32_t b2, uint32_t rbA, uint32_t lmA, int s, int e, bool cand) {
     bool stop = false;
     if (m.sw_perfect) {  // one probe: 16-bit slot -> word id, then the record is compared
         const uint32_t id = reinterpret_cast<const uint16_t*>(swt)[(h * m.sw_mul) >> m.sw_shift];
         const uint4 w = sww[id ? id - 1u : 0u];
         const bool c = cand && id != 0u;
         stop = c && (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
-        if (c && w.x == (n | 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, lmask, s, e);
+        if (c && w.x == (n | 0x80000000u)) stop = long_stop_word_equal_s(m.sw_pool + w.y, rbA, lmA, s, e);
     } else if (m.sw_cap) {
         const uint32_t swmask = (uint32_t)m.sw_cap - 1u;
         const uint32_t e1 = swt[h & swmask], e2 = swt[(h >> 10) & swmask];
@@ -95,11 +102,11 @@ __device__ __forceinline__ bool stop_probe(const Model& m, const uint32_t* swt, 
             const uint32_t ent = m1 ? e1 : e2;
             uint4 w = sww[(ent & 0xFFFFu) - 1u];
             stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
-            if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, lmask, s, e);
+            if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal_s(m.sw_pool + w.y, rbA, lmA, s, e);
             if (!stop && m1 && m2) {  // fingerprint collision in the first slot: look at the second
                 w = sww[(e2 & 0xFFFFu) - 1u];
                 stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
-                if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, lmask, s, e);
+                if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal_s(m.sw_pool + w.y, rbA, lmA, s, e);
             }
         }
     }
@@ -165,14 +172,14 @@ __device__ __forceinline__ uint32_t mmk(uint32_t k) { return rotl_c<15>(k * 0xcc
 // for featurize and dense classifiers, where every token is probed.  The record of slot value `id` sits at
 // swwA + 16 (id - 1); id = 0 (no word) reads the 16 bytes before the records -- valid shared memory -- and is masked out.
 __device__ __forceinline__ bool stop_probe_s(const Model& m, uint32_t swtA, uint32_t swwA, uint32_t h, uint32_t n, uint32_t b0, uint32_t b1,
-                                             uint32_t b2, const uint8_t* rb, const uint32_t* lmask, int s, int e, bool cand) {
+                                             uint32_t b2, uint32_t rbA, uint32_t lmA, int s, int e, bool cand) {
     bool stop = false;
     if (m.sw_perfect) {
         const uint32_t id = lds_u16(swtA + 2u * ((h * m.sw_mul) >> m.sw_shift));
         const uint4 w = lds_v4(swwA + 16u * id - 16u);
         const bool c = cand && id != 0u;
         stop = c && (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
-        if (c && w.x == (n | 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, lmask, s, e);
+        if (c && w.x == (n | 0x80000000u)) stop = long_stop_word_equal_s(m.sw_pool + w.y, rbA, lmA, s, e);
     } else if (m.sw_cap) {
         const uint32_t swmask = (uint32_t)m.sw_cap - 1u;
         const uint32_t e1 = lds_u32(swtA + 4u * (h & swmask)), e2 = lds_u32(swtA + 4u * ((h >> 10) & swmask));
@@ -181,11 +188,11 @@ __device__ __forceinline__ bool stop_probe_s(const Model& m, uint32_t swtA, uint
             const uint32_t ent = m1 ? e1 : e2;
             uint4 w = lds_v4(swwA + 16u * (ent & 0xFFFFu) - 16u);
             stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
-            if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, lmask, s, e);
+            if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal_s(m.sw_pool + w.y, rbA, lmA, s, e);
             if (!stop && m1 && m2) {  // fingerprint collision in the first slot: look at the second
                 w = lds_v4(swwA + 16u * (e2 & 0xFFFFu) - 16u);
                 stop = (w.x == n) && (w.y == b0 && w.z == b1 && w.w == b2);
-                if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal(m.sw_pool + w.y, rb, lmask, s, e);
+                if ((w.x & 0x7FFFFFFFu) == n && (w.x & 0x80000000u)) stop = long_stop_word_equal_s(m.sw_pool + w.y, rbA, lmA, s, e);
             }
         }
     }
@@ -349,6 +356,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
     const uint32_t swtA = lutA + LUT_BYTES, swwA = swtA + (uint32_t)m.sw_tab_bytes();  // !DTS: the stop-word tables
     const uint32_t rawA = smem_u32(wmem);
     const uint32_t tokA = rawA + (uint32_t)offsetof(MainWarp, tok);
+    const uint32_t lmA = rawA + (uint32_t)offsetof(MainWarp, lmask);
     const uint32_t cntA = rawA + (uint32_t)sizeof(MainWarp);
 
     if (threadIdx.x < 13) {
@@ -729,7 +737,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                     const uint32_t key = lds_u32(dtkA + slot4);
                     bool hit = ins && ((key ^ fi) & 0x7FFFFFFFu) == 0u;
                     if (DTS == 2 && __any_sync(FULL, hit && (int)key < 0)) {  // a stop word maps to this split feature: is the token one?
-                        if (hit && (int)key < 0 && !empty) hit = !stop_probe(m, m.sw_tab, m.sw_words, h, n, b0, b1, b2, rb, S.lmask, s, e, true);
+                        if (hit && (int)key < 0 && !empty) hit = !stop_probe(m, m.sw_tab, m.sw_words, h, n, b0, b1, b2, rbA, lmA, s, e, true);
                     }
                     if (hit) red_add_u32(cntA + slot4, 1u);
                 } else {
@@ -738,10 +746,10 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
                         ins = ins && ((fw.x >> (fi & 31)) & 1u);           // can the classifier see this feature at all?
                         const bool chk = ins && !empty && ((fw.y >> (fi & 31)) & 1u);
                         if (__any_sync(FULL, chk)) {                       // ... and a stop word maps to it: is the token one?
-                            if (chk) ins = !stop_probe_s(m, swtA, swwA, h, n, b0, b1, b2, rb, S.lmask, s, e, true);
+                            if (chk) ins = !stop_probe_s(m, swtA, swwA, h, n, b0, b1, b2, rbA, lmA, s, e, true);
                         }
                     } else if (m.sw_cap) {
-                        ins = ins && !stop_probe_s(m, swtA, swwA, h, n, b0, b1, b2, rb, S.lmask, s, e, valid && !empty);
+                        ins = ins && !stop_probe_s(m, swtA, swwA, h, n, b0, b1, b2, rbA, lmA, s, e, valid && !empty);
                     }
                     bool isnew = false;
                     if (csr_list) {  // append the bucket; the end of the dialogue orders and counts the list

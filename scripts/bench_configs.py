@@ -282,6 +282,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="c1,c3,c4,c5")
     ap.add_argument("--c3-rows", type=int, default=10_000_000, help="total dialogues (split over ranks)")
+    ap.add_argument("--c1-rows", type=int, default=1_000_000, help="dialogues of C1's device-resident pass")
     ap.add_argument("--train-rows", type=int, default=10_000_000)
     ap.add_argument("--train-trees", type=int, default=100)
     ap.add_argument("--train-depth", type=int, default=10)
@@ -305,6 +306,8 @@ def main():
     for name in a.configs.split(","):
         if name == "c3":
             res = run_c3(ctx, a.c3_rows)
+        elif name == "c1":
+            res = run_c1(ctx, a.c1_rows)
         elif name == "c5":
             res = run_c5(ctx, a.train_rows, a.train_trees, a.train_depth)
         else:
