@@ -329,8 +329,11 @@ __device__ int csr_sorted_emit(const RowArgs& a, uint32_t listA, int n, uint32_t
 // CTA shape (row_warps); DTS: small-decision-tree path (MODE_DT with Model::dt_heap_on, hashing trick) -- per-warp counters
 // instead of a count table, nothing is ever deferred for size; 2 = some split feature is also a stop word's bucket;
 // POW2: HashingTF with a power-of-two numFeatures (bucket = hash & mask).
-template <int MODE, bool CLEAN, int TL, int DTS, bool POW2>
+template <int MODE, bool CLEAN, int TL, int VAR, bool POW2>
 __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(const RowArgs a, const int cta_bytes, const int warp_bytes) {
+    constexpr int DTS = (VAR == 1 || VAR == 2) ? VAR : 0;  // VAR: 0 count table, 1 / 2 small decision tree, 3 token list (featurize)
+    constexpr bool csr_list = VAR == 3;                    // featurize: token list instead of a count table
+    static_assert(VAR != 3 || MODE == MODE_CSR, "the token list is featurize's");
     constexpr int ROW_WARPS = row_warps(TL);
     constexpr uint32_t FULL = 0xFFFFFFFFu;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -389,7 +392,6 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
     const uint8_t* text = a.text;
     const bool binary = m.binary != 0;
     const uint32_t fmask = (uint32_t)(m.num_features - 1);
-    const bool csr_list = MODE == MODE_CSR && m.csr_list != 0;      // featurize: token list instead of a count table
     const int bin_shift = max(__popc(fmask) - 8, 0);                // (POW2) bucket -> one of 256 bins
     const int list_cap = min(CSR_LIST_MAX, (8 << TL) / 4);          // keys the table area holds
     unsigned long long* tab = stab;  // TL == 9: may move to the warp's wide table in global memory
@@ -864,13 +866,14 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
 // ------------------------------------------------------------------------------------------------
 // launcher
 // ------------------------------------------------------------------------------------------------
-template <int MODE, bool CLEAN, int TL, int DTS, bool POW2>
+template <int MODE, bool CLEAN, int TL, int VAR, bool POW2>
 static cudaError_t launch_k(fd_handle* h, const RowArgs& a, cudaStream_t st) {
+    constexpr int DTS = (VAR == 1 || VAR == 2) ? VAR : 0;
     constexpr int NW = row_warps(TL);
     const size_t cta_bytes = LUT_BYTES + (DTS ? (((size_t)4 << a.m.dt_log2) + 160 * 8) : ((a.m.sw_smem_bytes() + 15) & ~(size_t)15));
     const size_t warp_bytes = sizeof(MainWarp) + (DTS ? ((size_t)4 << a.m.dt_log2) : ((size_t)8 << TL));
     const size_t smem = cta_bytes + (size_t)NW * warp_bytes;
-    auto kern = k_main<MODE, CLEAN, TL, DTS, POW2>;
+    auto kern = k_main<MODE, CLEAN, TL, VAR, POW2>;
     // shared-memory opt-in and occupancy are looked up once per (kernel, size) and kept in the handle
     int occ = 0;
     for (const auto& c : h->launch_cfg)
@@ -890,6 +893,13 @@ static cudaError_t launch_k(fd_handle* h, const RowArgs& a, cudaStream_t st) {
     return cudaGetLastError();
 }
 
+// count-table kernel, or featurize's token-list variant when the model allows it (Model::csr_list)
+template <int MODE, bool CLEAN, int TL, bool POW2>
+static cudaError_t launch_generic(fd_handle* h, const RowArgs& a, cudaStream_t st) {
+    if (MODE == MODE_CSR && a.m.csr_list) return launch_k<MODE, CLEAN, TL, MODE == MODE_CSR ? 3 : 0, POW2>(h, a, st);
+    return launch_k<MODE, CLEAN, TL, 0, POW2>(h, a, st);
+}
+
 template <int MODE, bool CLEAN, bool POW2>
 static cudaError_t launch_shapes(fd_handle* h, const RowArgs& a0, cudaStream_t st) {
     RowArgs a = a0;
@@ -905,15 +915,15 @@ static cudaError_t launch_shapes(fd_handle* h, const RowArgs& a0, cudaStream_t s
         // finds out from the offsets whether its shape is the one that runs (the other exits at once)
         const float keep = (MODE == MODE_LINEAR && a.m.filt_on) ? a.m.lr_keep : 1.0f;
         if (a.host_bytes >= 0) {
-            if (shape_for(a.host_bytes, a.n_rows, keep) == 8) return launch_k<MODE, CLEAN, 8, 0, POW2>(h, a, st);
+            if (shape_for(a.host_bytes, a.n_rows, keep) == 8) return launch_generic<MODE, CLEAN, 8, POW2>(h, a, st);
         } else {
             a.pick_shape = 1;
             a.pick_keep = keep;
-            const cudaError_t e = launch_k<MODE, CLEAN, 8, 0, POW2>(h, a, st);
+            const cudaError_t e = launch_generic<MODE, CLEAN, 8, POW2>(h, a, st);
             if (e != cudaSuccess) return e;
         }
     }
-    return launch_k<MODE, CLEAN, 9, 0, POW2>(h, a, st);
+    return launch_generic<MODE, CLEAN, 9, POW2>(h, a, st);
 }
 
 cudaError_t launch_main_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st) {
