@@ -345,14 +345,27 @@ def default_subset_batch(seed: int, n_features: int, k: int, device):
     return fn
 
 
-def _units_device(col_len, feats):
-    """Device version of :func:`_units`."""
+def _seg_len(nodes_per_tree: float, row_nnz: float, subset_fraction: float) -> int:
+    """Column entries per work unit of a level whose trees have ``nodes_per_tree`` open nodes.  The column walks gather
+    state[tree, row] at scattered rows; the ~9,500 units in flight should belong to one or two trees, whose state rows then
+    stay in the L2.  A tree's walk visits about nodes x nnz x (features per node / features) entries, so near the root the
+    units have to be short for one tree to fill the machine; deep levels keep SEG_LEN."""
+    want = nodes_per_tree * row_nnz * subset_fraction * 850.0
+    seg = 256
+    while seg * 2 <= want and seg < SEG_LEN:
+        seg *= 2
+    return seg
+
+
+def _units_device(col_len, feats, seg_len: int = SEG_LEN):
+    """Device version of :func:`_units` -> (unit_item, unit_seg, seg_len)."""
     import torch
+    SEG_LEN = int(seg_len)
     nseg = (col_len[feats] + SEG_LEN - 1) // SEG_LEN
     unit_item = torch.repeat_interleave(torch.arange(feats.numel(), dtype=torch.int32, device=feats.device), nseg)
     first = torch.cumsum(nseg, 0) - nseg
     unit_seg = (torch.arange(unit_item.numel(), dtype=torch.int64, device=feats.device) - torch.repeat_interleave(first, nseg)).to(torch.int32)
-    return unit_item, unit_seg
+    return unit_item, unit_seg, SEG_LEN
 
 
 # ------------------------------------------------------------------------------------------ backend
@@ -408,11 +421,12 @@ class CudaTreeBackend:
         node_id << 8 | bag weight."""
         colptr, rowidx, bins = csc
         it_t, it_n, it_f = items
-        u_item, u_seg = units
+        u_item, u_seg = units[0], units[1]
+        seg_len = int(units[2]) if len(units) > 2 else SEG_LEN
         n_items = it_t.numel()
         hist = self.torch.empty((n_items, 32, 2), dtype=self.torch.int32, device=self.device)
         self.h.call("fd_rf_histogram", _lib.ptr(colptr), _lib.ptr(rowidx), _lib.ptr(bins), _lib.ptr(state), state.shape[1], n_items,
-                    _lib.ptr(it_t), _lib.ptr(it_n), _lib.ptr(it_f), u_item.numel(), _lib.ptr(u_item), _lib.ptr(u_seg), SEG_LEN,
+                    _lib.ptr(it_t), _lib.ptr(it_n), _lib.ptr(it_f), u_item.numel(), _lib.ptr(u_item), _lib.ptr(u_seg), seg_len,
                     _lib.ptr(hist), self._st())
         return hist
 
@@ -432,10 +446,11 @@ class CudaTreeBackend:
     def advance(self, csc, state, level_base, splits, units, action):
         colptr, rowidx, bins = csc
         s_t, s_n, s_f, s_b = splits
-        u_item, u_seg = units
+        u_item, u_seg = units[0], units[1]
+        seg_len = int(units[2]) if len(units) > 2 else SEG_LEN
         self.h.call("fd_rf_advance", _lib.ptr(colptr), _lib.ptr(rowidx), _lib.ptr(bins), _lib.ptr(state), state.shape[1],
                     state.shape[0], int(level_base), s_t.numel(), _lib.ptr(s_t), _lib.ptr(s_n), _lib.ptr(s_f), _lib.ptr(s_b),
-                    u_item.numel(), _lib.ptr(u_item), _lib.ptr(u_seg), SEG_LEN, _lib.ptr(action), self._st())
+                    u_item.numel(), _lib.ptr(u_item), _lib.ptr(u_seg), seg_len, _lib.ptr(action), self._st())
 
 
 # ------------------------------------------------------------------------------------------ trainer
@@ -444,8 +459,9 @@ def _dist():
     return dist if dist.is_available() and dist.is_initialized() else None
 
 
-def _units(col_len: np.ndarray, feats: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
-    """One work unit per SEG_LEN entries of each item's column -> (unit_item int32[], unit_seg int32[])."""
+def _units(col_len: np.ndarray, feats: np.ndarray, seg_len: int = SEG_LEN) -> Tuple[np.ndarray, np.ndarray]:
+    """One work unit per ``seg_len`` entries of each item's column -> (unit_item int32[], unit_seg int32[])."""
+    SEG_LEN = int(seg_len)
     nseg = (col_len[feats] + SEG_LEN - 1) // SEG_LEN
     unit_item = np.repeat(np.arange(feats.size, dtype=np.int32), nseg)
     first = np.cumsum(nseg) - nseg
@@ -612,6 +628,9 @@ class ForestTrainer:
             if aidx.size == 0:
                 break
             sp_parts, child_parts = [], []
+            # work-unit length of this level's column walks (see _seg_len)
+            open_trees = max(1, int(np.unique(lt[aidx]).size))
+            seg_len = _seg_len(aidx.size / open_trees, float(idx.numel()) / max(1, n_local), min(1.0, k / float(self.F)))
             g0 = 0
             while g0 < aidx.size:
                 # ---- one node group: items = node x feature subset (features without thresholds dropped), on the device
@@ -646,7 +665,7 @@ class ForestTrainer:
                 tt = self._tick("subsets+items", tt)
                 if items[2].numel() == 0:
                     continue
-                units = _units_device(d_col_len, items[2].long())
+                units = _units_device(d_col_len, items[2].long(), seg_len)
                 tt = self._tick("units", tt)
                 hist = self.b.histogram(csc, state, items, units)
                 tt = self._tick("kernel:histogram", tt)
@@ -678,7 +697,8 @@ class ForestTrainer:
             action = np.full((self.T, base), -1, dtype=np.int32)
             action[sp[:, 0], sp[:, 1] - base] = np.where(bin_of_zero[sp[:, 2]] <= sp[:, 3], 2 * sp[:, 1], 2 * sp[:, 1] + 1)
             d_sp = tuple(torch.from_numpy(np.ascontiguousarray(sp[:, c])).to(dev) for c in range(4))
-            units = tuple(torch.from_numpy(a).to(dev) for a in _units(col_len, sp[:, 2]))
+            adv_seg = _seg_len(sp.shape[0] / max(1, int(np.unique(sp[:, 0]).size)), 1.0, 1.0 / 16.0)  # (a split feature's column: ~1/16 of the rows)
+            units = _units_device(d_col_len, d_sp[2].long(), adv_seg)
             self.b.advance(csc, state, base, d_sp, units, torch.from_numpy(action).to(dev))
             # next level: the two children of every split node, left then right, in split order
             ct = np.concatenate([c[0] for c in child_parts])
