@@ -41,6 +41,7 @@ SIGNATURES = {
     "fd_transform_noalloc": (C.c_int, [_p, _p, _p, _i64, _u32, _p, _p, _p, _p, _p]),
     "fd_eval_auc_roc": (C.c_int, [_p, _p, _i64, _p, _i64, _i32, _p, _p]),
     "fd_eval_confusion2": (C.c_int, [_p, _p, _p, _i64, _p, _p]),
+    "fd_idf_scale": (C.c_int, [_p, _p, _p, _i64, _p, _i32, _p]),
     "fd_workspace_bytes": (_i64, [_p, _i64]),
     "fd_csc_scratch_bytes": (_i64, [_p, _i64, _i32]),
     "fd_reserve": (C.c_int, [_p, _i64]),

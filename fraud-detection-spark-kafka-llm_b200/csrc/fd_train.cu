@@ -63,6 +63,12 @@ __global__ void k_doc_freq(const int32_t* __restrict__ idx, const double* __rest
         if (val[k] > 0.0) atomicAdd(df + idx[k], 1ULL);
 }
 
+// ---- IDFModel.transform on a CSR matrix already on the device: val[k] *= idf[idx[k]] (one exact fp64 multiply) ----------
+__global__ void k_idf_scale(const int32_t* __restrict__ idx, double* __restrict__ val, long long nnz, const double* __restrict__ idf) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += stride) val[k] = __dmul_rn(val[k], __ldg(idf + idx[k]));
+}
+
 // ---- bagging: Poisson(rate) bootstrap weights + weighted class totals of the root ------------------------
 // One thread draws 16 consecutive rows of one tree (one 16-byte store).  u = top 32 bits of splitmix64(key) with
 // key = seed, tree, row; the draw is the number of CDF thresholds <= u (thresholds precomputed on the host).
@@ -419,6 +425,19 @@ int fd_doc_freq(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int
     long long g = (nnz + 255) / 256;
     if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
     k_doc_freq<<<(unsigned)g, 256, 0, st>>>(idx_dev, val_dev, nnz, reinterpret_cast<unsigned long long*>(out_doc_freq_dev));
+    h->launches += 1;
+    FD_CUDA(h, cudaGetLastError());
+    return FD_OK;
+}
+
+int fd_idf_scale(fd_handle* h, const int32_t* idx_dev, double* val_dev, int64_t nnz, const double* idf_dev, int32_t num_features, void* stream) {
+    if (!h) return FD_ERR_INVALID;
+    if (nnz < 0 || num_features <= 0 || (nnz > 0 && (!idx_dev || !val_dev || !idf_dev))) return set_err(h, FD_ERR_INVALID, "bad fd_idf_scale arguments");
+    if (nnz == 0) return FD_OK;
+    FD_CUDA(h, cudaSetDevice(h->device));
+    long long g = (nnz + 255) / 256;
+    if (g > (long long)h->sm_count * 32) g = (long long)h->sm_count * 32;
+    k_idf_scale<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>(idx_dev, val_dev, nnz, idf_dev);
     h->launches += 1;
     FD_CUDA(h, cudaGetLastError());
     return FD_OK;

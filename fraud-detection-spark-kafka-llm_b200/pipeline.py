@@ -423,7 +423,9 @@ class Pipeline:
                     dist.all_reduce(nd)
                 st = st.fit_from_doc_freq(df.cpu().numpy(), int(nd.item()))
             fitted.append(st)
-            val.mul_(torch.from_numpy(st.idf).to(dev)[idx])  # IDFModel.transform: one exact fp64 multiply
+            d_idf = torch.from_numpy(np.ascontiguousarray(st.idf, dtype=np.float64)).to(dev)
+            tf_model.handle(device).call("fd_idf_scale", _lib.ptr(idx), _lib.ptr(val), int(idx.numel()), _lib.ptr(d_idf), int(nf),
+                                         _stream_ptr(dev))  # IDFModel.transform: one exact fp64 multiply per entry, in place
             tt = tick("idf fit+transform", tt)
         if est:
             c = est[0]

@@ -101,6 +101,11 @@ int fd_hash_terms(const uint8_t* terms, const int32_t* offs, int32_t n, int32_t 
  * idf = log((numDocs + 1) / (docFreq + 1)).  Asynchronous. */
 int fd_doc_freq(fd_handle* h, const int32_t* idx_dev, const double* val_dev, int64_t nnz, int32_t num_features,
                 int64_t* out_doc_freq_dev, void* stream);
+/* IDFModel.transform on a CSR matrix that is already on the device (the step of Pipeline.fit between IDF.fit and the
+ * classifier's fit, fraud_detection_spark.py:85-91): val[k] *= idf_dev[idx[k]], one exact fp64 multiply, in place.
+ * idf_dev: f64[num_features] on the device.  Asynchronous. */
+int fd_idf_scale(fd_handle* h, const int32_t* idx_dev, double* val_dev, int64_t nnz, const double* idf_dev, int32_t num_features,
+                 void* stream);
 /* IDFModel.idf (stages/3_IDF_58bd96296a82/data): dense f64[num_features]; NULL removes the stage. */
 int fd_set_idf(fd_handle* h, const double* idf, int32_t num_features);
 /* Binomial LogisticRegressionModel (stages/4_LogisticRegression_65ef69d6dfd9): dense coefficient
