@@ -185,11 +185,19 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_histogram(const int64_t*
         const long long c0 = colptr[f] + (long long)unit_seg[u] * seg_len;
         const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
         const uint32_t* st = state + (long long)t * n_rows;
-        for (long long e = c0 + lane; e < c1; e += 32) {
-            const uint32_t rl = __ldcs(rowidx + e);
-            const uint32_t s = ld_keep_u32(st + (rl & 0x7FFFFFFFu), keep);
-            const uint32_t w = s & 255u;
-            if ((s >> 8) == node && w) atomicAdd(&h[(int)__ldcs(bin + e) * 2 + (int)(rl >> 31)], w);
+        // four entries per lane and trip: the walk is bound by the latency of the dependent state gather, so the loads of
+        // a trip are issued together (entries past the segment's end read its last entry and are masked out)
+        for (long long e0 = c0 + lane; e0 < c1; e0 += 128) {
+            uint32_t rl[4], s[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) rl[j] = __ldcs(rowidx + min(e0 + 32 * j, c1 - 1));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) s[j] = ld_keep_u32(st + (rl[j] & 0x7FFFFFFFu), keep);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t w = s[j] & 255u;
+                if ((s[j] >> 8) == node && w && e0 + 32 * j < c1) atomicAdd(&h[(int)__ldcs(bin + e0 + 32 * j) * 2 + (int)(rl[j] >> 31)], w);
+            }
         }
         __syncwarp();
         unsigned int* g = hist + (size_t)item * (HB * 2);
@@ -314,10 +322,16 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_advance_explicit(const i
         uint32_t* st = state + (long long)split_tree[s] * n_rows;
         const long long c0 = colptr[f] + (long long)unit_seg[u] * seg_len;
         const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
-        for (long long e = c0 + lane; e < c1; e += 32) {
-            const uint32_t r = __ldcs(rowidx + e) & 0x7FFFFFFFu;
-            const uint32_t v = ld_keep_u32(st + r, keep);
-            if ((v >> 8) == node) st_keep_u32(st + r, ((((int)__ldcs(bin + e) <= sb) ? 2u * node : 2u * node + 1u) << 8) | (v & 255u), keep);
+        for (long long e0 = c0 + lane; e0 < c1; e0 += 128) {  // (four entries per lane and trip, as in the histogram walk)
+            uint32_t r[4], v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) r[j] = __ldcs(rowidx + min(e0 + 32 * j, c1 - 1)) & 0x7FFFFFFFu;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = ld_keep_u32(st + r[j], keep);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if ((v[j] >> 8) == node && e0 + 32 * j < c1)
+                    st_keep_u32(st + r[j], ((((int)__ldcs(bin + e0 + 32 * j) <= sb) ? 2u * node : 2u * node + 1u) << 8) | (v[j] & 255u), keep);
         }
     }
 }
