@@ -1,6 +1,7 @@
 """GPU training parity: the fd_rf_* kernels (through the C-ABI) grow exactly the oracle's trees given the same
 bins, bag weights and feature subsets (identical splits on identical bins -- BASELINE.json north_star), and
 Pipeline.fit produces a model whose held-out AUC shows the planted signal."""
+import ctypes as C
 import importlib
 import os
 
@@ -304,3 +305,29 @@ def test_bag_weight_overflow_guard(fd):
     bag = torch.full((2, n), 255, dtype=torch.uint8, device="cuda")
     with pytest.raises(ValueError, match="2\\^31"):
         tr.fit(rowptr, idx, val, labels, bag_weights=bag, subset_fn=lambda t, node: np.arange(4, dtype=np.int32))
+
+
+def test_doc_freq_private_vectors_at_scale(fd):
+    """fd_doc_freq on a matrix large enough for its private count vectors (>= 2^22 entries): equals a bincount of the
+    entries with a positive value, with a heavily skewed feature distribution and some non-positive values."""
+    import torch
+    lib = importlib.import_module("fraud-detection-spark-kafka-llm_b200._lib")
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev)
+    g.manual_seed(5)
+    nnz, nf = 6_000_000, 5000
+    idx = (torch.rand(nnz, generator=g, device=dev) ** 4 * nf).to(torch.int32).clamp_(max=nf - 1)   # a few very hot features
+    val = torch.rand(nnz, generator=g, device=dev, dtype=torch.float64) - 0.1                   # ~10% not positive
+    val[::1000] = 0.0
+    h = lib.Handle(0)
+    df = torch.empty(nf, dtype=torch.int64, device=dev)
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    h.call("fd_doc_freq", lib.ptr(idx), lib.ptr(val), nnz, nf, lib.ptr(df), st)
+    exp = torch.bincount(idx[val > 0].long(), minlength=nf)
+    assert torch.equal(df, exp)
+    assert int(df.max()) > 100_000
+    # and the scaling kernel: one exact multiply per entry
+    idf = torch.rand(nf, generator=g, device=dev, dtype=torch.float64)
+    want = val * idf[idx.long()]
+    h.call("fd_idf_scale", lib.ptr(idx), lib.ptr(val), nnz, lib.ptr(idf), nf, st)
+    assert torch.equal(val, want)
