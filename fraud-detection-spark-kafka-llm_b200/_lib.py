@@ -48,10 +48,10 @@ SIGNATURES = {
     "fd_launch_count": (_i64, [_p]),
     "fd_bin_csr": (C.c_int, [_p, _p, _p, _i64, _p, _p, _p, _p]),
     "fd_csc_build": (C.c_int, [_p, _p, _p, _p, _p, _i64, _i64, _i32, _p, _p, _p, _i64, _p]),
-    "fd_rf_histogram": (C.c_int, [_p, _p, _p, _p, _p, _i64, _i32, _p, _p, _p, _i32, _p, _p, _i32, _p, _p]),
+    "fd_rf_histogram": (C.c_int, [_p, _p, _p, _p, _p, _i64, _i32, _p, _p, _p, _p, _i32, _p, _p, _i32, _p, _p]),
     "fd_rf_best_split": (C.c_int, [_p, _p, _i32, _p, _p, _p, _p, _p, _i32, _f64, _p, _p, _p, _p, _p, _p]),
     "fd_rf_bag_poisson": (C.c_int, [_p, C.c_uint64, _f64, _i32, _i64, _p, _p, _p, _p]),
-    "fd_rf_advance": (C.c_int, [_p, _p, _p, _p, _p, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _i32, _p, _p, _i32, _p, _p]),
+    "fd_rf_advance": (C.c_int, [_p, _p, _p, _p, _p, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _i32, _p, _p, _i32, _p, _p]),
 }
 
 _lib = None

@@ -174,6 +174,16 @@ __device__ __forceinline__ void st_keep_u32(uint32_t* p, uint32_t v, uint64_t po
 // [32 bins][2 classes]; the non-zero cells are then added to the item's global histogram.
 // Per entry ONE gather: the row's label rides in bit 31 of the column's row index, and the row's node id and
 // bag weight share one word, state[tree, row] = node_id << 8 | bag_weight.
+// Rows that do NOT hold a split feature follow the node's default child.  They are not rewritten: their state keeps naming
+// the ancestor they last moved to by an explicit entry, and a node of the current level is told how many of its nearest
+// ancestors lead to it by default links only (`chain`, kept by the trainer: 0 for the non-default child).  A row whose
+// state is one of those ancestors sits in the node -- it was never moved explicitly on the way, or its state would name a
+// later node.  Heap numbering: the ancestor d levels up is node >> d.  (This replaces a pass over all of state per level.)
+__device__ __forceinline__ bool in_node(uint32_t state_node, uint32_t node, int node_depth, uint32_t chain) {
+    const int d = node_depth - (31 - __clz(state_node));
+    return (unsigned)d <= chain && (node >> d) == state_node;
+}
+
 constexpr int WALK_WARPS = 2;
 constexpr int WALK_ILP = 4;    // entries per lane and trip of a column walk  // warps per CTA of the column walks (see the scheduling note below)
 
@@ -187,7 +197,8 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_histogram(const int64_t*
                                                       long long n_rows, int n_units, const int32_t* __restrict__ unit_item,
                                                       const int32_t* __restrict__ unit_seg, int seg_len,
                                                       const int32_t* __restrict__ item_tree, const int32_t* __restrict__ item_node,
-                                                      const int32_t* __restrict__ item_feat, unsigned int* __restrict__ hist) {
+                                                      const int32_t* __restrict__ item_feat, const int32_t* __restrict__ item_chain,
+                                                      unsigned int* __restrict__ hist) {
     __shared__ unsigned int sh[WALK_WARPS][HB * 2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned int* h = sh[warp];
@@ -200,6 +211,9 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_histogram(const int64_t*
         const int item = unit_item[u];
         const int t = item_tree[item], f = item_feat[item];
         const uint32_t node = (uint32_t)item_node[item];
+        // a row is in `node` when its state names the node or one of the node's `chain` nearest ancestors (see in_node)
+        const uint32_t chain = item_chain ? (uint32_t)item_chain[item] : 0u;
+        const int dn = 31 - __clz(node);
         const long long c0 = colptr[f] + (long long)unit_seg[u] * seg_len;
         const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
         const uint32_t* st = state + (long long)t * n_rows;
@@ -214,7 +228,7 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_histogram(const int64_t*
 #pragma unroll
             for (int j = 0; j < WALK_ILP; ++j) {
                 const uint32_t w = s[j] & 255u;
-                if ((s[j] >> 8) == node && w && e0 + 32 * j < c1) atomicAdd(&h[(int)__ldcs(bin + e0 + 32 * j) * 2 + (int)(rl[j] >> 31)], w);
+                if (in_node(s[j] >> 8, node, dn, chain) && w && e0 + 32 * j < c1) atomicAdd(&h[(int)__ldcs(bin + e0 + 32 * j) * 2 + (int)(rl[j] >> 31)], w);
             }
         }
         __syncwarp();
@@ -329,7 +343,8 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_advance_explicit(const i
                                                              long long n_rows, int n_units, const int32_t* __restrict__ unit_item,
                                                              const int32_t* __restrict__ unit_seg, int seg_len,
                                                              const int32_t* __restrict__ split_tree, const int32_t* __restrict__ split_node,
-                                                             const int32_t* __restrict__ split_feat, const int32_t* __restrict__ split_bin) {
+                                                             const int32_t* __restrict__ split_feat, const int32_t* __restrict__ split_bin,
+                                                             const int32_t* __restrict__ split_chain) {
     const int lane = threadIdx.x & 31;
     const uint64_t keep = l2_keep_policy();
     const int u = blockIdx.x * WALK_WARPS + (threadIdx.x >> 5);
@@ -337,6 +352,8 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_advance_explicit(const i
         const int s = unit_item[u];
         const uint32_t node = (uint32_t)split_node[s];
         const int f = split_feat[s], sb = split_bin[s];
+        const uint32_t chain = split_chain ? (uint32_t)split_chain[s] : 0u;
+        const int dn = 31 - __clz(node);
         uint32_t* st = state + (long long)split_tree[s] * n_rows;
         const long long c0 = colptr[f] + (long long)unit_seg[u] * seg_len;
         const long long c1 = min((long long)colptr[f + 1], c0 + (long long)seg_len);
@@ -348,7 +365,7 @@ __global__ void __launch_bounds__(WALK_WARPS * 32) k_rf_advance_explicit(const i
             for (int j = 0; j < WALK_ILP; ++j) v[j] = ld_keep_u32(st + r[j], keep);
 #pragma unroll
             for (int j = 0; j < WALK_ILP; ++j)
-                if ((v[j] >> 8) == node && e0 + 32 * j < c1)
+                if (in_node(v[j] >> 8, node, dn, chain) && e0 + 32 * j < c1)
                     st_keep_u32(st + r[j], ((((int)__ldcs(bin + e0 + 32 * j) <= sb) ? 2u * node : 2u * node + 1u) << 8) | (v[j] & 255u), keep);
         }
     }
@@ -492,7 +509,7 @@ int fd_idf_scale(fd_handle* h, const int32_t* idx_dev, double* val_dev, int64_t 
 
 int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowidx_dev, const uint8_t* bin_dev,
                     const uint32_t* state_dev, int64_t n_rows, int32_t n_items, const int32_t* item_tree_dev, const int32_t* item_node_dev, const int32_t* item_feat_dev,
-                    int32_t n_units, const int32_t* unit_item_dev, const int32_t* unit_seg_dev, int32_t seg_len,
+                    const int32_t* item_chain_dev, int32_t n_units, const int32_t* unit_item_dev, const int32_t* unit_seg_dev, int32_t seg_len,
                     uint32_t* out_hist_dev, void* stream) {
     if (!h) return FD_ERR_INVALID;
     if (n_items < 0 || n_units < 0 || seg_len <= 0 || !out_hist_dev) return set_err(h, FD_ERR_INVALID, "bad fd_rf_histogram arguments");
@@ -502,7 +519,7 @@ int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const uint32_t* row
     if (n_units == 0) return FD_OK;
     const int g = (n_units + WALK_WARPS - 1) / WALK_WARPS;
     k_rf_histogram<<<g, WALK_WARPS * 32, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, state_dev, n_rows, n_units, unit_item_dev,
-                                      unit_seg_dev, seg_len, item_tree_dev, item_node_dev, item_feat_dev, out_hist_dev);
+                                      unit_seg_dev, seg_len, item_tree_dev, item_node_dev, item_feat_dev, item_chain_dev, out_hist_dev);
     h->launches += 1;
     FD_CUDA(h, cudaGetLastError());
     return FD_OK;
@@ -558,8 +575,8 @@ int fd_rf_best_split(fd_handle* h, const uint32_t* hist_dev, int32_t n_nodes, co
 int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowidx_dev, const uint8_t* bin_dev,
                   uint32_t* state_dev, int64_t n_rows, int32_t n_trees, int32_t level_base, int32_t n_split_nodes,
                   const int32_t* split_tree_dev, const int32_t* split_node_dev, const int32_t* split_feat_dev,
-                  const int32_t* split_bin_dev, int32_t n_units, const int32_t* unit_item_dev, const int32_t* unit_seg_dev,
-                  int32_t seg_len, const int32_t* action_dev, void* stream) {
+                  const int32_t* split_bin_dev, const int32_t* split_chain_dev, int32_t n_units, const int32_t* unit_item_dev,
+                  const int32_t* unit_seg_dev, int32_t seg_len, const int32_t* action_dev, void* stream) {
     if (!h) return FD_ERR_INVALID;
     if (n_split_nodes < 0 || n_units < 0 || seg_len <= 0 || level_base <= 0) return set_err(h, FD_ERR_INVALID, "bad fd_rf_advance arguments");
     if (n_split_nodes == 0) return FD_OK;
@@ -568,8 +585,12 @@ int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowid
     if (n_units > 0) {
         const int g = (n_units + WALK_WARPS - 1) / WALK_WARPS;
         k_rf_advance_explicit<<<g, WALK_WARPS * 32, 0, st>>>(colptr_dev, rowidx_dev, bin_dev, state_dev, n_rows, n_units, unit_item_dev, unit_seg_dev,
-                                                 seg_len, split_tree_dev, split_node_dev, split_feat_dev, split_bin_dev);
+                                                 seg_len, split_tree_dev, split_node_dev, split_feat_dev, split_bin_dev, split_chain_dev);
         h->launches += 1;
+    }
+    if (!action_dev) {  // default moves are implied by the chain lengths (in_node): no pass over state
+        FD_CUDA(h, cudaGetLastError());
+        return FD_OK;
     }
     long long g2 = (n_rows + 255) / 256;
     const long long cap = std::max<long long>(1, (long long)h->sm_count * 16 / std::max(1, n_trees));

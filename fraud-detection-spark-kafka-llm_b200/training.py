@@ -371,6 +371,7 @@ def _units_device(col_len, feats, seg_len: int = SEG_LEN):
 # ------------------------------------------------------------------------------------------ backend
 class CudaTreeBackend:
     """Thin adapter: torch CUDA tensors in, C-ABI calls (fd_bin_csr, fd_rf_*) on the current stream."""
+    lazy_default = True   # rows without a split feature are not rewritten; items / splits carry chain lengths instead
 
     def __init__(self, handle: _lib.Handle):
         import torch
@@ -420,13 +421,15 @@ class CudaTreeBackend:
         """csc = (colptr i64, rowidx i32 with the row's label in bit 31, bin u8); state i32 [n_trees, n_rows] =
         node_id << 8 | bag weight."""
         colptr, rowidx, bins = csc
-        it_t, it_n, it_f = items
+        it_t, it_n, it_f = items[0], items[1], items[2]
+        it_j = items[3] if len(items) > 3 else None   # chain lengths (None: every row's state names its node)
         u_item, u_seg = units[0], units[1]
         seg_len = int(units[2]) if len(units) > 2 else SEG_LEN
         n_items = it_t.numel()
         hist = self.torch.empty((n_items, 32, 2), dtype=self.torch.int32, device=self.device)
         self.h.call("fd_rf_histogram", _lib.ptr(colptr), _lib.ptr(rowidx), _lib.ptr(bins), _lib.ptr(state), state.shape[1], n_items,
-                    _lib.ptr(it_t), _lib.ptr(it_n), _lib.ptr(it_f), u_item.numel(), _lib.ptr(u_item), _lib.ptr(u_seg), seg_len,
+                    _lib.ptr(it_t), _lib.ptr(it_n), _lib.ptr(it_f), _lib.ptr(it_j) if it_j is not None else None, u_item.numel(), _lib.ptr(u_item),
+                    _lib.ptr(u_seg), seg_len,
                     _lib.ptr(hist), self._st())
         return hist
 
@@ -445,12 +448,14 @@ class CudaTreeBackend:
 
     def advance(self, csc, state, level_base, splits, units, action):
         colptr, rowidx, bins = csc
-        s_t, s_n, s_f, s_b = splits
+        s_t, s_n, s_f, s_b = splits[0], splits[1], splits[2], splits[3]
+        s_j = splits[4] if len(splits) > 4 else None  # chain lengths: with them the default moves need no pass (action unused)
         u_item, u_seg = units[0], units[1]
         seg_len = int(units[2]) if len(units) > 2 else SEG_LEN
         self.h.call("fd_rf_advance", _lib.ptr(colptr), _lib.ptr(rowidx), _lib.ptr(bins), _lib.ptr(state), state.shape[1],
                     state.shape[0], int(level_base), s_t.numel(), _lib.ptr(s_t), _lib.ptr(s_n), _lib.ptr(s_f), _lib.ptr(s_b),
-                    u_item.numel(), _lib.ptr(u_item), _lib.ptr(u_seg), seg_len, _lib.ptr(action), self._st())
+                    _lib.ptr(s_j) if s_j is not None else None, u_item.numel(), _lib.ptr(u_item), _lib.ptr(u_seg), seg_len,
+                    _lib.ptr(action) if s_j is None else None, self._st())
 
 
 # ------------------------------------------------------------------------------------------ trainer
@@ -612,6 +617,10 @@ class ForestTrainer:
         lt = np.arange(self.T, dtype=np.int32)                  # this level's nodes: tree ...
         ln = np.ones(self.T, dtype=np.int32)                    # ... heap id (root 1) ...
         ls = np.ascontiguousarray(root, dtype=np.float64)       # ... class counts [m, 2]
+        # ... and, for backends that do not rewrite the rows that follow a default child (lazy_default), how many of the
+        # node's nearest ancestors lead to it by default links only
+        lazy = bool(getattr(self.b, "lazy_default", False))
+        lj = np.zeros(self.T, dtype=np.int32)
         levels = []
         hist_bytes = allreduce_calls = 0
         for depth in range(self.max_depth + 1):
@@ -645,10 +654,12 @@ class ForestTrainer:
                     ok = d_nsplits[sub] > 0
                     cnt = ok.sum(dim=1)
                     items = (torch.repeat_interleave(grp_t, cnt), torch.repeat_interleave(grp_n, cnt), sub[ok].to(torch.int32))
+                    if lazy:
+                        items = items + (torch.repeat_interleave(torch.from_numpy(lj[gi]).to(dev), cnt),)
                     d_ptr = torch.zeros(g1 - g0 + 1, dtype=torch.int32, device=dev)
                     d_ptr[1:] = torch.cumsum(cnt, 0)
                 else:
-                    it_t, it_n, it_f, ptr = [], [], [], [0]
+                    it_t, it_n, it_f, it_j, ptr = [], [], [], [], [0]
                     while g1 < aidx.size and (g1 == g0 or ptr[-1] < MAX_ITEMS_PER_GROUP):
                         t, n = int(lt[aidx[g1]]), int(ln[aidx[g1]])
                         feats = np.asarray(subset_fn(t, n), dtype=np.int32)
@@ -656,10 +667,11 @@ class ForestTrainer:
                         it_t.append(np.full(feats.size, t, np.int32))
                         it_n.append(np.full(feats.size, n, np.int32))
                         it_f.append(feats)
+                        it_j.append(np.full(feats.size, lj[aidx[g1]], np.int32))
                         ptr.append(ptr[-1] + feats.size)
                         g1 += 1
                     gi = aidx[g0:g1]
-                    items = tuple(torch.from_numpy(np.concatenate(x)).to(dev) for x in (it_t, it_n, it_f))
+                    items = tuple(torch.from_numpy(np.concatenate(x)).to(dev) for x in ((it_t, it_n, it_f, it_j) if lazy else (it_t, it_n, it_f)))
                     d_ptr = torch.tensor(ptr, dtype=torch.int32, device=dev)
                 g0 = g1
                 tt = self._tick("subsets+items", tt)
@@ -689,7 +701,7 @@ class ForestTrainer:
                 l_thr[wi] = thr[thr_ptr[f] + sb]
                 l_gain[wi] = bg[won]
                 sp_parts.append(np.stack([lt[wi], ln[wi], f, sb], 1).astype(np.int32))
-                child_parts.append((lt[wi], ln[wi], left[won], right[won]))
+                child_parts.append((lt[wi], ln[wi], left[won], right[won], lj[wi]))
             tt = self._tick("host:grow", tt)
             sp = np.concatenate(sp_parts) if sp_parts else np.zeros((0, 4), np.int32)
             if sp.shape[0] == 0:
@@ -697,9 +709,12 @@ class ForestTrainer:
             action = np.full((self.T, base), -1, dtype=np.int32)
             action[sp[:, 0], sp[:, 1] - base] = np.where(bin_of_zero[sp[:, 2]] <= sp[:, 3], 2 * sp[:, 1], 2 * sp[:, 1] + 1)
             d_sp = tuple(torch.from_numpy(np.ascontiguousarray(sp[:, c])).to(dev) for c in range(4))
+            pj = np.concatenate([c[4] for c in child_parts]).astype(np.int32)   # the split nodes' own chain lengths
+            if lazy:
+                d_sp = d_sp + (torch.from_numpy(pj).to(dev),)
             adv_seg = _seg_len(sp.shape[0] / max(1, int(np.unique(sp[:, 0]).size)), 1.0, 1.0 / 16.0)  # (a split feature's column: ~1/16 of the rows)
             units = _units_device(d_col_len, d_sp[2].long(), adv_seg)
-            self.b.advance(csc, state, base, d_sp, units, torch.from_numpy(action).to(dev))
+            self.b.advance(csc, state, base, d_sp, units, None if lazy else torch.from_numpy(action).to(dev))
             # next level: the two children of every split node, left then right, in split order
             ct = np.concatenate([c[0] for c in child_parts])
             cn = np.concatenate([c[1] for c in child_parts])
@@ -708,6 +723,8 @@ class ForestTrainer:
             lt = np.repeat(ct, 2).astype(np.int32)
             ln = np.stack([2 * cn, 2 * cn + 1], 1).reshape(-1).astype(np.int32)
             ls = np.stack([cl, cr], 1).reshape(-1, 2).astype(np.float64)
+            dflt = action[sp[:, 0], sp[:, 1] - base]                             # each split node's default child
+            lj = np.stack([np.where(dflt == 2 * cn, pj + 1, 0), np.where(dflt == 2 * cn + 1, pj + 1, 0)], 1).reshape(-1).astype(np.int32)
             tt = self._tick("kernel:advance", tt)
         cat = [np.concatenate([lv[c] for lv in levels]) for c in range(7)]
         trees = trees_from_levels(self.T, cat[0], cat[1], cat[2], cat[3], cat[4], cat[5], cat[6], self.prune)

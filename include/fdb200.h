@@ -229,11 +229,14 @@ int fd_rf_bag_poisson(fd_handle* h, uint64_t seed, double rate, int32_t n_trees,
  * the node: hist[item, bin, label] += weight.  state u32[n_trees, n_rows] = node_id << 8 | bag_weight (heap
  * numbering, root 1; node ids below 2^24) -- one gather per column entry.  Long columns are cut into segments of
  * seg_len entries: UNIT u covers segment unit_seg[u] of item unit_item[u]'s column (one warp per unit).
+ * item_chain int32[n_items] (or NULL = all zero): how many of the node's nearest ancestors reach it through DEFAULT links
+ * only -- a row whose state still names one of them sits in the node (rows without a split feature are never rewritten, see
+ * fd_rf_advance).
  * out_hist u32[n_items, 32, 2] is zeroed by the call.  Rows WITHOUT the feature are not added here:
  * fd_rf_best_split adds them after the cross-rank sum (NCCL all-reduce of out_hist by the caller). */
 int fd_rf_histogram(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowidx_dev, const uint8_t* bin_dev,
                     const uint32_t* state_dev, int64_t n_rows, int32_t n_items, const int32_t* item_tree_dev,
-                    const int32_t* item_node_dev, const int32_t* item_feat_dev, int32_t n_units,
+                    const int32_t* item_node_dev, const int32_t* item_feat_dev, const int32_t* item_chain_dev, int32_t n_units,
                     const int32_t* unit_item_dev, const int32_t* unit_seg_dev, int32_t seg_len, uint32_t* out_hist_dev,
                     void* stream);
 /* binsToBestSplit for a node group (histograms already summed over ranks).  node_item_ptr int32[n_nodes+1]
@@ -252,12 +255,14 @@ int fd_rf_best_split(fd_handle* h, const uint32_t* hist_dev, int32_t n_nodes, co
  * (split_tree/node/feat/bin int32[n_split_nodes]) rows holding the feature go to 2*node when bin <= split_bin else
  * 2*node+1 (units as in fd_rf_histogram, unit_item indexes the split list); every other row of that level follows
  * action int32[n_trees, level_base]: the child id that bin_of_zero selects, or -1 when its node became a leaf (the
- * row keeps its id). */
+ * row keeps its id).  action_dev = NULL skips that pass over all of state: the rows keep naming the node they last reached
+ * through an explicit entry, and the caller passes chain lengths (split_chain int32[n_split_nodes] here, item_chain to
+ * fd_rf_histogram; NULL = zeros) so that the walks recognise them -- what training.ForestTrainer does. */
 int fd_rf_advance(fd_handle* h, const int64_t* colptr_dev, const uint32_t* rowidx_dev, const uint8_t* bin_dev,
                   uint32_t* state_dev, int64_t n_rows, int32_t n_trees, int32_t level_base, int32_t n_split_nodes,
                   const int32_t* split_tree_dev, const int32_t* split_node_dev, const int32_t* split_feat_dev,
-                  const int32_t* split_bin_dev, int32_t n_units, const int32_t* unit_item_dev, const int32_t* unit_seg_dev,
-                  int32_t seg_len, const int32_t* action_dev, void* stream);
+                  const int32_t* split_bin_dev, const int32_t* split_chain_dev, int32_t n_units, const int32_t* unit_item_dev,
+                  const int32_t* unit_seg_dev, int32_t seg_len, const int32_t* action_dev, void* stream);
 
 #ifdef __cplusplus
 }
