@@ -331,3 +331,26 @@ def test_doc_freq_private_vectors_at_scale(fd):
     want = val * idf[idx.long()]
     h.call("fd_idf_scale", lib.ptr(idx), lib.ptr(val), nnz, lib.ptr(idf), nf, st)
     assert torch.equal(val, want)
+
+
+@pytest.mark.parametrize("num_features", [300, 1 << 18, (1 << 25) + 3])
+def test_csc_build_equals_stable_sort(fd, num_features):
+    """fd_csc_build (a radix sort over just the bits a feature id can have) against a stable argsort by feature id:
+    columns in feature order, rows ascending inside a column, label in bit 31 of the row word."""
+    lib = importlib.import_module("fraud-detection-spark-kafka-llm_b200._lib")
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev)
+    g.manual_seed(3)
+    n_rows, per_row = 20_000, 12
+    base = torch.randint(0, num_features, (n_rows, 1), generator=g, device=dev)
+    idx = ((base + torch.arange(per_row, device=dev) * 7919) % num_features).sort(dim=1).values.to(torch.int32).reshape(-1)
+    rowptr = torch.arange(n_rows + 1, device=dev, dtype=torch.int64) * per_row
+    bins = torch.randint(0, 32, (idx.numel(),), generator=g, device=dev).to(torch.uint8)
+    labels = (torch.rand(n_rows, generator=g, device=dev) < 0.3).to(torch.uint8)
+    backend = training.CudaTreeBackend(lib.Handle(0))
+    rowidx, cbins = backend.csc_build(rowptr, idx, bins, labels, num_features)
+    order = torch.argsort(idx, stable=True)
+    row_of = torch.arange(n_rows, device=dev).repeat_interleave(per_row)
+    want = (row_of | (labels.long() << 31).repeat_interleave(per_row))[order]
+    assert torch.equal(rowidx.view(torch.int32).long() & 0xFFFFFFFF, want)
+    assert torch.equal(cbins, bins[order])
