@@ -156,7 +156,11 @@ int fd_transform(fd_handle* h, const uint8_t* text_dev, const int64_t* offs_dev,
 int fd_status(fd_handle* h, void* stream);
 /* Same with HOST buffers (pinned memory recommended): the call chunks the batch, overlaps the
  * host->device copies, the kernels and the device->host copies on internal streams, and returns when
- * the three result columns are complete in host memory.  text_host needs no padding or alignment. */
+ * the three result columns are complete in host memory.  text_host needs no padding or alignment.
+ * A micro-batch (at most 65,536 dialogues and 8 MiB of text) whose five buffers are all pinned (page-locked, mapped)
+ * host memory, text_host 16-byte aligned, is not copied: the kernels read the text and offsets and write the columns in
+ * place over PCIe -- same results, fewer driver calls on the latency path (utils/agent_api.py:158 one dialogue at a time,
+ * app_ui.py:195-226 one poll at a time).  Environment FDB200_DIRECT_HOST=0 (read at fd_create) turns that off. */
 int fd_transform_host(fd_handle* h, const uint8_t* text_host, const int64_t* offs_host, int64_t n_rows,
                       uint32_t flags, double* out_pred_host, double* out_prob_host, double* out_raw_host);
 /* No counterpart in the reference (nor in Spark): the fused transform for callers that cannot allocate device
