@@ -25,14 +25,14 @@ struct __align__(16) Node {
 constexpr uint32_t EMPTY_KEY = 0xFFFFFFFFu;
 
 // control block at the start of the workspace (device memory, written by kernels)
-constexpr size_t CTRL_CLEAR_BYTES = 20;  // tmp_cursor, big_count, big2_count, tmp_overflow
+constexpr size_t CTRL_CLEAR_BYTES = 24;  // tmp_cursor, big_count, big2_count, tmp_overflow, next_item
 struct Ctrl {
     unsigned long long tmp_cursor;  // entries allocated in the CSR staging buffer
     unsigned int big_count;         // dialogues deferred to the medium wide-table kernel (list grows from the front)
     unsigned int big2_count;        // dialogues deferred to the large wide-table kernel (list grows from the back)
     unsigned int tmp_overflow;      // staging buffer was too small
+    unsigned int next_item;         // micro-batches: dialogues handed out after every warp's first (RowArgs::dyn_rows)
     int status;                     // sticky device-side status (FD_OK / FD_ERR_LIMIT); NOT cleared per call
-    int shape;                      // (unused: the kernel shape is derived from the offsets by the kernels themselves)
     unsigned int pad[1];
 };
 

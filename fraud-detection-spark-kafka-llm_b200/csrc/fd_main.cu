@@ -557,7 +557,13 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
             n_lo = (int)(cursor - n_wbase);
             n_lbmin = 0;
         } else {
-            n_item = item + stride;
+            if (a.dyn_rows) {
+                unsigned int nx = 0;
+                if (lane == 0) nx = atomicAdd(&a.ctrl->next_item, 1u);
+                n_item = stride + (long long)__shfl_sync(FULL, nx, 0);  // (the first `stride` dialogues were handed out by warp index)
+            } else {
+                n_item = item + stride;
+            }
             have_next = n_item < n_items;
             if (have_next) {
                 n_row = n_item;
@@ -926,7 +932,13 @@ static cudaError_t launch_shapes(fd_handle* h, const RowArgs& a0, cudaStream_t s
     return launch_generic<MODE, CLEAN, 9, POW2>(h, a, st);
 }
 
-cudaError_t launch_main_rows(fd_handle* h, int mode, const RowArgs& a, cudaStream_t st) {
+// micro-batches take their dialogues dynamically: one atomic per dialogue on one address is nothing for a few thousand
+// dialogues and would serialise a batch of a million
+constexpr long long DYN_ROWS_MAX = 1 << 16;
+
+cudaError_t launch_main_rows(fd_handle* h, int mode, const RowArgs& a0, cudaStream_t st) {
+    RowArgs a = a0;
+    a.dyn_rows = a.n_rows <= DYN_ROWS_MAX ? 1 : 0;
     const bool c = (a.flags & FD_FLAG_CLEAN) != 0;
     const bool p2 = a.m.mod_pow2 && !a.m.vocab_cap;
 #define FD_DISPATCH(M)                                                                                                 \

@@ -68,6 +68,8 @@ struct RowArgs {
     int pick_shape;  // 1: both main-kernel shapes are launched and each decides from the mean dialogue length whether it runs
     float pick_keep; // ... scaled by the fraction of a dialogue's terms that reach the count table (sparse LogisticRegression)
     long long host_bytes;  // total text bytes when the caller knows them on the host (the shape is then picked there), else -1
+    int dyn_rows;    // micro-batches: after its first dialogue a warp takes the next one from Ctrl::next_item (a warp that
+                     // holds a 20 KB dialogue then gets no second one while others sit idle); set by launch_main_rows
     unsigned long long* big_tabs;    // table pool of the medium wide-table variant
     unsigned long long* big2_tabs;   // ... of the large one (may equal big_tabs when the two variants run one after the other)
     unsigned long long* spill_tabs;  // SPILL_SLOTS slots, or nullptr (no spilling: overflowing dialogues are deferred)
