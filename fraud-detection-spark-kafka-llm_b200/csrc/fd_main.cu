@@ -557,7 +557,7 @@ __global__ void __launch_bounds__(32 * row_warps(TL), TL == 8 ? 2 : 3) k_main(co
             n_lo = (int)(cursor - n_wbase);
             n_lbmin = 0;
         } else {
-            if (a.dyn_rows) {
+            if (TL == 9 && a.dyn_rows) {  // (the 512-slot shape is the one micro-batches run in; the large-batch shape stays static)
                 unsigned int nx = 0;
                 if (lane == 0) nx = atomicAdd(&a.ctrl->next_item, 1u);
                 n_item = stride + (long long)__shfl_sync(FULL, nx, 0);  // (the first `stride` dialogues were handed out by warp index)
