@@ -17,7 +17,9 @@
  *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Compute calls are
  *    asynchronous on that stream unless stated otherwise.
  *  - a handle is bound to one device, owns a growable device workspace, and is not re-entrant;
- *    distinct handles are independent.
+ *    distinct handles are independent.  The compute calls of ONE handle share that workspace
+ *    (fd_transform*, fd_featurize_*, fd_vocab_count, fd_doc_freq): issue them on one stream, or
+ *    order the streams yourself, so that two of them never run at the same time.
  *  - packed text: `text` = all dialogues' UTF-8 bytes back to back, `offs` = int64[n_rows+1] byte
  *    offsets (offs[0] may be > 0).  `text` must be 16-byte aligned and readable up to the next
  *    multiple of 16 past offs[n_rows] (the kernels stage 16-byte-aligned windows with TMA bulk
