@@ -87,6 +87,7 @@ int prepare_fused(fd_handle* h) {
     Model& m = h->m;
     h->fused_dirty = false;
     m.int_walk = 0;
+    m.dense_on = 0;
     m.dt_small = 0;
     m.dt_heap_on = 0;
     m.filt_on = 0;
@@ -107,6 +108,7 @@ int prepare_fused(fd_handle* h) {
     const bool has_idf = !h->host_idf.empty();
     const std::vector<Node>& q = h->host_nodes;
     std::vector<int32_t> cs(q.size(), 0);
+    std::vector<char> never(q.size(), 0);  // the node's test can never send a dialogue right (weight 0)
     for (const auto& nd : q) {
         if (nd.feat < 0) continue;
         const double w = has_idf ? h->host_idf[(size_t)nd.feat] : 1.0;
@@ -114,7 +116,7 @@ int prepare_fused(fd_handle* h) {
         if (!(w >= 0.0)) return FD_OK;  // negative or NaN weight: keep the floating-point walk
         long long c;
         if (!(thr >= 0.0)) c = -1;                       // also NaN: "x <= NaN" is never true
-        else if (w == 0.0) c = 0x7FFFFFFF;               // x is 0.0 whatever the count
+        else if (w == 0.0) { c = 0x7FFFFFFF; never[(size_t)(&nd - q.data())] = 1; }  // x is 0.0 whatever the count
         else {
             const double g = std::floor(thr / w);
             c = g >= 2147483646.0 ? 2147483646LL : (long long)g;
@@ -161,6 +163,39 @@ int prepare_fused(fd_handle* h) {
     int rc = upload(h, reinterpret_cast<uint32_t**>(&m.nodes_s), sec.data(), sec.size());
     if (rc) return rc;
     m.int_walk = 1;
+    // dense walks (Model::dense_on): forest-local feature ids, byte counts
+    if (h->dense_want && m.kind != FD_KIND_DT && m.num_features <= (1 << 22)) {
+        std::vector<uint32_t> feats;
+        bool fits = true;
+        for (size_t n = 0; n < q.size(); ++n) {
+            if (q[n].feat < 0) continue;
+            feats.push_back((uint32_t)q[n].feat);
+            if (!never[n] && cs[n] > 254) fits = false;  // a count saturated at 255 must still decide every test
+        }
+        std::sort(feats.begin(), feats.end());
+        feats.erase(std::unique(feats.begin(), feats.end()), feats.end());
+        if (fits && !feats.empty() && feats.size() <= (size_t)DENSE_MAX) {
+            std::vector<uint16_t> local((size_t)m.num_features, (uint16_t)0xFFFFu);
+            for (size_t i = 0; i < feats.size(); ++i) local[feats[i]] = (uint16_t)i;
+            std::vector<uint32_t> secl(sec);
+            for (size_t n = 0; n < q.size(); ++n) {
+                if (is_leaf((int)n)) continue;
+                uint32_t* w = &secl[8 * n];
+                w[0] = local[(size_t)q[n].feat];
+                if (never[n]) w[5] = 255u;
+                for (int side = 0; side < 2; ++side) {
+                    const int c = q[n].child + side;
+                    if (is_leaf(c)) continue;
+                    w[1 + side] = (uint32_t)local[(size_t)q[(size_t)c].feat] | (w[1 + side] & 0x80000000u);
+                    if (never[(size_t)c]) w[6 + side] = 255u;
+                }
+            }
+            rc = upload(h, reinterpret_cast<uint32_t**>(&m.nodes_l), secl.data(), secl.size());
+            if (!rc) rc = upload(h, &m.f_local, local.data(), local.size());
+            if (rc) return rc;
+            m.dense_on = 1;
+        }
+    }
     // decision tree: count only the split features (Model::dt_small)
     if (m.kind == FD_KIND_DT) {
         std::vector<uint32_t> feats;
@@ -292,6 +327,8 @@ int fd_create(int device, fd_handle** out) {
         h->sm_count = prop.multiProcessorCount;
         if (!prop.canMapHostMemory || !prop.unifiedAddressing) h->direct_host = 0;
     }
+    const char* dw = getenv("FDB200_DENSE_WALK");
+    if (dw && dw[0] == '0') h->dense_want = 0;
     const char* e = getenv("FDB200_DIRECT_HOST");
     if (e && e[0] == '0') h->direct_host = 0;
     *out = h;
@@ -316,6 +353,8 @@ int fd_destroy(fd_handle* h) {
     cudaFree(m.dt_out);
     cudaFree(m.nodes);
     cudaFree(m.nodes_s);
+    cudaFree(m.nodes_l);
+    cudaFree(m.f_local);
     cudaFree(m.nodes_dt);
     cudaFree(m.dt_tab);
     cudaFree(m.roots);

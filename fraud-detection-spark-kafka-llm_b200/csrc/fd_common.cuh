@@ -25,6 +25,7 @@ struct __align__(16) Node {
 constexpr uint32_t EMPTY_KEY = 0xFFFFFFFFu;
 
 // control block at the start of the workspace (device memory, written by kernels)
+constexpr int DENSE_MAX = 2048;          // forest-local feature ids of the dense walks (Model::dense_on): bytes of the vector
 constexpr size_t CTRL_CLEAR_BYTES = 24;  // tmp_cursor, big_count, big2_count, tmp_overflow, next_item
 struct Ctrl {
     unsigned long long tmp_cursor;  // entries allocated in the CSR staging buffer
@@ -95,6 +96,12 @@ struct Model {
     // child word; bit 31 of L.feat / L.child says that L's left / right child is a leaf (same for R).
     uint4* nodes_s = nullptr;
     int int_walk = 0;          // 1: the fused kernels walk nodes_s with integer compares
+    // forests over at most DENSE_MAX distinct split features whose count thresholds fit a byte: the end of a dialogue
+    // spreads its counts over a dense byte vector indexed by forest-local feature id (f_local: feature -> local id,
+    // 0xFFFF = not a split feature) and a node visit is one byte load; nodes_l = nodes_s with local ids
+    uint4* nodes_l = nullptr;
+    uint16_t* f_local = nullptr;
+    int dense_on = 0;
     // A decision tree splits on a handful of features (at most 2^depth - 1), and its prediction depends on the counts
     // of those features only.  When there are at most 63 of them the fused DT kernel keeps just those counts: a perfect
     // hash (f * dt_mul) >> dt_shift over 2^dt_log2 slots (dt_tab[slot] = the feature, ~0 = none) indexes per-warp
@@ -142,6 +149,7 @@ struct fd_handle {
     char* hbuf[3] = {nullptr, nullptr, nullptr};
     size_t hbuf_bytes[3] = {0, 0, 0};
     fd::Ctrl* pinned_ctrl = nullptr;
+    int dense_want = 1;   // forests may use the dense byte-count walk (FDB200_DENSE_WALK=0 keeps the lookup front)
     int direct_host = 1;  // fd_transform_host may read / write pinned caller buffers in place (FDB200_DIRECT_HOST=0 turns it off)
     // host copies needed to (re)build nodes_s when the idf vector or the forest changes
     std::vector<fd::Node> host_nodes;

@@ -227,6 +227,24 @@ __device__ __forceinline__ void build_fidx(const unsigned long long* tab, int lo
     __syncwarp();
 }
 
+// dense byte counts over forest-local feature ids (Model::dense_on): zeroed, then every entry of the dialogue's count table
+// whose feature the forest splits on stores min(count, 255) at its local id
+__device__ __forceinline__ void build_dense(const unsigned long long* tab, int log2cap, uint8_t* dense, const uint16_t* f_local, int lane) {
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = lane; i < DENSE_MAX / 16; i += 32) reinterpret_cast<uint4*>(dense)[i] = z;
+    __syncwarp();
+    const int cap = 1 << log2cap;
+    for (int i = lane; i < cap; i += 32) {
+        const unsigned long long e = tab[i];
+        const uint32_t k = (uint32_t)(e >> 32);
+        if (k != EMPTY_KEY) {
+            const uint32_t loc = __ldg(f_local + k);
+            if (loc != 0xFFFFu) dense[loc] = (uint8_t)min((uint32_t)e, 255u);
+        }
+    }
+    __syncwarp();
+}
+
 __device__ __forceinline__ uint32_t tab_lookup(const unsigned long long* tab, int log2cap, const uint16_t* fidx, uint32_t idx) {
     if (fidx == nullptr) return tab_lookup(tab, log2cap, idx);
     const uint32_t j = fidx[fidx_slot(idx)];
@@ -464,6 +482,22 @@ __device__ __forceinline__ void ldg_256(const uint4* p, uint4& a, uint4& b) {
                  : "l"(p));
 }
 
+// the same two-levels-per-record walk over nodes_l with the dense byte counts: a node visit is one byte load
+__device__ __forceinline__ int walk_tree_dense(const Model& m, const uint8_t* dense, int root) {
+    int n = root;
+    for (;;) {
+        uint4 q0, q1;
+        ldg_256(m.nodes_l + 2 * (size_t)n, q0, q1);
+        const bool r1 = (int)dense[q0.x] > (int)q1.y;
+        const uint32_t cf = r1 ? q0.z : q0.y, cc = r1 ? q1.x : q0.w;
+        const int ccs = (int)(r1 ? q1.w : q1.z);
+        if ((cf & 0x7FFFFFFFu) == 0x7FFFFFFFu) return (int)cc;  // the child is a leaf
+        const bool r2 = (int)dense[cf & 0x7FFFFFFFu] > ccs;
+        n = (int)(cc & 0x7FFFFFFFu) + (r2 ? 1 : 0);
+        if ((r2 ? cc : cf) >> 31) return n;                     // the grandchild is a leaf
+    }
+}
+
 // returns the node id of the leaf the dialogue's count table reaches from `root`
 __device__ __forceinline__ int walk_tree(const Model& m, const unsigned long long* tab, int log2cap, const uint16_t* fidx, int root,
                                          const uint32_t* dtc = nullptr) {  // dtc: the small-DT counters (records hold their slots)
@@ -515,9 +549,15 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, double* scratch2
                              long long row, int D, int lane) {
     const Model& m = a.m;  // scratch: the token-list area (2 KiB+), scratch2: the finished window buffer (1 KiB+); both free here
     const uint16_t* fidx = nullptr;
+    const uint8_t* dense = nullptr;
     if ((MODE == MODE_RF || MODE == MODE_GBT) && smem_tab && m.int_walk && m.n_trees >= 8) {
-        build_fidx(tab, log2cap, reinterpret_cast<uint16_t*>(scratch), lane);
-        fidx = reinterpret_cast<const uint16_t*>(scratch);
+        if (m.dense_on) {
+            build_dense(tab, log2cap, reinterpret_cast<uint8_t*>(scratch), m.f_local, lane);
+            dense = reinterpret_cast<const uint8_t*>(scratch);
+        } else {
+            build_fidx(tab, log2cap, reinterpret_cast<uint16_t*>(scratch), lane);
+            fidx = reinterpret_cast<const uint16_t*>(scratch);
+        }
         scratch = scratch2;
     }
     // sorted order of the compacted entries: tab[perm[i]] (register sort) or tab[i] (in-place sort)
@@ -574,7 +614,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, double* scratch2
         for (int b = 0; b < m.n_trees; b += 32) {
             const int t = b + lane;
             if (t < m.n_trees) {
-                const int n = walk_tree(m, tab, log2cap, fidx, __ldg(m.roots + t));
+                const int n = dense ? walk_tree_dense(m, dense, __ldg(m.roots + t)) : walk_tree(m, tab, log2cap, fidx, __ldg(m.roots + t));
                 const double2 st = __ldg(m.leaf2 + n);
                 scratch[lane] = st.x;
                 scratch[32 + lane] = st.y;
@@ -592,7 +632,7 @@ __device__ void row_epilogue(const RowArgs& a, double* scratch, double* scratch2
         for (int b = 0; b < m.n_trees; b += 32) {
             const int t = b + lane;
             if (t < m.n_trees) {
-                const int n = walk_tree(m, tab, log2cap, fidx, __ldg(m.roots + t));
+                const int n = dense ? walk_tree_dense(m, dense, __ldg(m.roots + t)) : walk_tree(m, tab, log2cap, fidx, __ldg(m.roots + t));
                 scratch[lane] = __dmul_rn(__ldg(&m.nodes[n].thr), __ldg(m.tree_w + t));
             }
             __syncwarp();

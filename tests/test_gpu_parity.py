@@ -551,3 +551,30 @@ def test_count_vectorizer_model_transform(fd, binary, tmp_path):
     again = fd.PipelineModel.load(str(tmp_path / "cv"))
     assert again.stages[2].vocabulary == vocab
     _check_scores(again.transform(rows), ora.transform(rows))
+
+
+@pytest.mark.parametrize("kind", ["rf", "gbt"])
+@pytest.mark.parametrize("case", ["dense", "lookup-front", "too-many-features", "large-thresholds"])
+def test_forest_walk_variants(fd, kind, case, monkeypatch):
+    """The forest epilogue has two node-visit forms: a dense byte vector of counts over forest-local feature ids (at most
+    2,048 distinct split features, count thresholds below 255) and the 16-bit lookup front over the dialogue's count table.
+    Same dialogues, same oracle, for: the dense form, the front forced by FDB200_DENSE_WALK=0, a forest with more distinct
+    split features than the dense form takes, and one whose thresholds ask for counts of several hundred (tiny idf)."""
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    rng = np.random.default_rng(31)
+    nf = 1 << 16
+    corpus = synth.SynthCorpus(n_words=6000, seed=5)
+    n_feat_words = 5000 if case == "too-many-features" else 300
+    feats = synth.hash_terms(corpus.words[corpus.n_stop:corpus.n_stop + n_feat_words] + [b""], nf)
+    idf = np.log(1001.0 / (rng.integers(0, 1000, size=nf) + 1.0))
+    if case == "large-thresholds":
+        idf = idf * 1e-3          # thresholds stay as drawn, so the count they ask for grows a thousandfold
+    if case == "lookup-front":
+        monkeypatch.setenv("FDB200_DENSE_WALK", "0")
+    depths = [7] * 40 if case == "too-many-features" else [6, 3, 8, 1, 5, 7, 2, 6, 4, 8, 5, 6]
+    model = _forest_with_idf(fd, kind, idf, depths, nf, feats, seed=8)
+    pk, _ = corpus.sample(600, tokens=120, device="cpu", seed=2)
+    rows = [bytes(pk.data.numpy()[pk.offs[i]:pk.offs[i + 1]]) for i in range(pk.n_rows)]
+    rows += [b"", b" ", (b"payment " * 400), (b"verify account " * 300)]      # repeated terms: counts in the hundreds
+    res = model.transform([r.decode() for r in rows])
+    _check_scores(res, oracle_for(model).transform(rows))
