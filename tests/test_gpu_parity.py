@@ -578,3 +578,61 @@ def test_forest_walk_variants(fd, kind, case, monkeypatch):
     rows += [b"", b" ", (b"payment " * 400), (b"verify account " * 300)]      # repeated terms: counts in the hundreds
     res = model.transform([r.decode() for r in rows])
     _check_scores(res, oracle_for(model).transform(rows))
+
+
+def test_feature_space_change_drops_idf_and_classifier(fd):
+    """A call that changes the feature space (another numFeatures) must not leave the IDF vector and the classifier of the
+    old space live: fd_transform answers FD_ERR_STATE until both are set again, and then scores in the new space."""
+    import ctypes as C
+    import torch
+    lib = importlib.import_module("fraud-detection-spark-kafka-llm_b200._lib")
+    synth = importlib.import_module("fraud-detection-spark-kafka-llm_b200.synth")
+    h = lib.Handle(0)
+    dev = torch.device("cuda", 0)
+    texts = [b"verify your account now", b"hello how are you", b"", b"account account payment"]
+    pk = fd.PackedText.from_strings([t.decode() for t in texts]).to_device(dev)
+    n = pk.n_rows
+    outs = [torch.empty(s_, dtype=torch.float64, device=dev) for s_ in ((n,), (n, 2), (n, 2))]
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+    def upload(nf, seed):
+        rng = np.random.default_rng(seed)
+        idf = rng.random(nf) + 0.5
+        coef = rng.standard_normal(nf)
+        h.call("fd_set_idf", lib.ptr(idf), nf)
+        h.call("fd_set_linear", lib.ptr(coef), nf, C.c_double(0.1), C.c_double(0.5))
+        return idf, coef
+
+    def margins(nf, idf, coef):
+        exp = []
+        for t in texts:
+            toks = t.decode().split(" ")
+            while len(toks) > 1 and toks[-1] == "":          # Java's split drops trailing empties; "" itself stays [""]
+                toks.pop()
+            cnt = {}
+            for w in toks:
+                f = int(synth.hash_terms([w.encode()], nf)[0])
+                cnt[f] = cnt.get(f, 0) + 1
+            m = 0.0
+            for f in sorted(cnt):
+                m += (cnt[f] * idf[f]) * coef[f]
+            exp.append(m + 0.1)
+        return np.asarray(exp)
+
+    def run():
+        h.call("fd_transform", lib.ptr(pk.data), lib.ptr(pk.offs), n, 1, lib.ptr(outs[0]), lib.ptr(outs[1]), lib.ptr(outs[2]), st)
+        torch.cuda.synchronize()
+        return outs[2][:, 1].cpu().numpy()
+
+    h.call("fd_set_hashing", 1000, 0)
+    idf, coef = upload(1000, 1)
+    assert np.array_equal(run(), margins(1000, idf, coef))
+    h.call("fd_set_hashing", 50000, 0)                       # a larger space: the old vectors would be read out of bounds
+    with pytest.raises(lib.FdError) as e:
+        run()
+    assert "-4" in str(e.value)                              # FD_ERR_STATE
+    h.call("fd_set_idf", lib.ptr(np.ones(50000)), 50000)
+    with pytest.raises(lib.FdError):
+        run()                                                # the classifier is still missing
+    idf, coef = upload(50000, 2)
+    assert np.array_equal(run(), margins(50000, idf, coef))
