@@ -636,3 +636,20 @@ def test_feature_space_change_drops_idf_and_classifier(fd):
         run()                                                # the classifier is still missing
     idf, coef = upload(50000, 2)
     assert np.array_equal(run(), margins(50000, idf, coef))
+
+
+@pytest.mark.parametrize("words", [[""], [], ["", ""]])
+def test_degenerate_stop_word_lists(fd, shipped_model_dir, words):
+    """A stop-word list that holds nothing but the empty string (or nothing at all) has no word table on the device: the
+    kernels must not probe one.  Featurize and the fused LogisticRegression transform against the oracle."""
+    base = fd.PipelineModel.load(shipped_model_dir)
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"),
+              fd.StopWordsRemover(inputCol="words", outputCol="filtered_words", stopWords=words, caseSensitive=False)] + list(base.stages[2:])
+    model = fd.PipelineModel(stages)
+    texts = messy_texts(200, seed=4) + ["", " ", "a  b", "the the  the"]
+    ora = oracle_for(model)
+    rowptr, idx, val = model.featurize(texts)
+    for t, (ix, vl) in zip(texts, csr_rows(rowptr, idx, val)):
+        eix, evl, _, _ = ora.featurize(t.encode())
+        assert ix == eix and vl == evl, repr(t[:50])
+    _check_scores(model.transform(texts), ora.transform([t.encode() for t in texts]))
