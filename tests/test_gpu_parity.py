@@ -653,3 +653,34 @@ def test_degenerate_stop_word_lists(fd, shipped_model_dir, words):
         eix, evl, _, _ = ora.featurize(t.encode())
         assert ix == eix and vl == evl, repr(t[:50])
     _check_scores(model.transform(texts), ora.transform([t.encode() for t in texts]))
+
+
+def test_featurize_finish_after_another_call_is_refused(fd, shipped_model_dir):
+    """fd_featurize_begin stages its rows in the handle's workspace; a transform (or a document-frequency count) in between
+    reuses that memory, so the pending fd_featurize_finish must fail with FD_ERR_STATE instead of emitting a corrupt CSR --
+    and a fresh begin / finish pair works again."""
+    import ctypes as C
+    import torch
+    lib = importlib.import_module("fraud-detection-spark-kafka-llm_b200._lib")
+    model = fd.PipelineModel.load(shipped_model_dir)
+    h = model.handle()
+    dev = torch.device("cuda", h.device)
+    texts = messy_texts(300, seed=6)
+    pk = fd.PackedText.from_strings(texts).to_device(dev)
+    n = pk.n_rows
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    nnz = C.c_int64(0)
+    h.call("fd_featurize_begin", lib.ptr(pk.data), lib.ptr(pk.offs), n, 1, C.byref(nnz), st)
+    assert nnz.value > 0
+    model.transform(texts)                                   # reuses the workspace
+    rowptr = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    idx = torch.empty(nnz.value, dtype=torch.int32, device=dev)
+    val = torch.empty(nnz.value, dtype=torch.float64, device=dev)
+    with pytest.raises(lib.FdError) as e:
+        h.call("fd_featurize_finish", lib.ptr(rowptr), lib.ptr(idx), lib.ptr(val), nnz.value, st)
+    assert "-4" in str(e.value)
+    ora = oracle_for(model)
+    r2, i2, v2 = model.featurize(texts)
+    for t, (ix, vl) in zip(texts[:50], csr_rows(r2, i2, v2)):
+        eix, evl, _, _ = ora.featurize(t.encode())
+        assert ix == eix and vl == evl
