@@ -684,3 +684,29 @@ def test_featurize_finish_after_another_call_is_refused(fd, shipped_model_dir):
     for t, (ix, vl) in zip(texts[:50], csr_rows(r2, i2, v2)):
         eix, evl, _, _ = ora.featurize(t.encode())
         assert ix == eix and vl == evl
+
+
+def test_over_limit_status_survives_workspace_growth(fd):
+    """fd_transform is asynchronous: a dialogue over the size limit is only recorded in the device-side status word.  A
+    larger batch that makes the workspace grow (free + allocate) before anybody asked for the status must not lose it."""
+    import torch
+    lib = importlib.import_module("fraud-detection-spark-kafka-llm_b200._lib")
+    rng = np.random.default_rng(3)
+    nf = 1 << 18
+    stages = [fd.Tokenizer(inputCol="clean_text", outputCol="words"),
+              fd.HashingTF(inputCol="words", outputCol="features", numFeatures=nf),
+              fd.LogisticRegressionModel(rng.normal(0.0, 1.0, size=nf), 0.1)]
+    model = fd.PipelineModel(stages)
+    letters = rng.integers(97, 123, size=(70000, 7), dtype=np.uint8)
+    huge = b" ".join(bytes(r) for r in letters).decode()     # ~61k distinct buckets: over the limit of about 49k
+    h = model.handle(0)
+    before = int(h.lib.fd_workspace_bytes(h.h, 3))
+    model.transform(["fine one", huge, "fine two"])          # (device output: no status read)
+    big = ["row %d of a batch that needs a larger workspace" % i for i in range(300_000)]
+    assert int(h.lib.fd_workspace_bytes(h.h, len(big))) > before
+    res = model.transform(big)
+    assert not torch.isnan(res["prediction"]).any()
+    with pytest.raises(fd.FdError) as e:
+        h.call("fd_status", None)
+    assert e.value.code == lib.FD_ERR_LIMIT
+    h.call("fd_status", None)                                # reported once, then clear
